@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""
+bench.py — batched SafeLife env-steps/s on B200 (BASELINE.json metric), one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Workload (BASELINE.json configs[1]): append-still 26x26 benchmark levels, 4096 lockstep envs per
+GPU, seeded random actions; one "step" = one fused SafeLifeEnv.step (execute_action + advance_board
+on board and goals + points/performance reward + exit colours) over one batch of 4096 envs.
+To keep the timed region HBM-honest the bench cycles through a RING of independent 4096-env
+batches whose total state is > 2x the 126 MB L2, so every step reads state that has been evicted.
+
+N > 1 (torchrun): envs shard by index, 4096 per GPU (weak scaling); the only collective is the
+NCCL all-reduce of the statistics vector at the end of the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ENVS_PER_GPU = 4096
+H = W = 26
+BYTES_PER_ENV_STEP = 8 * H * W + 32  # 4 B per cell-update, board + goals, + scalars
+L2_BYTES = 126 * 1024 * 1024
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+                "samples": len(sm)}
+
+
+def append_still_levels():
+    from tests import golden_util as gu
+    return gu.levels("append-still")
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the reference's advance_board.c (oracle/_ref) + C port of the Python rule code
+# ---------------------------------------------------------------------------------------------
+def cpu_arm(n_envs, steps, warmup, threads):
+    from oracle import slo
+
+    lv = append_still_levels()
+    kind = "port"
+    if slo.have_ref():
+        slo.use_reference_advance(True)
+    env = slo.OracleBatchEnv(slo.OraclePool(**lv), np.arange(n_envs) % 100, seed=0, threads=threads)
+    rng = np.random.RandomState(2)
+    acts = rng.randint(9, size=(steps + warmup, n_envs))
+    for t in range(warmup):
+        env.step(acts[t])
+    t0 = time.perf_counter()
+    for t in range(warmup, warmup + steps):
+        env.step(acts[t])
+    dt = time.perf_counter() - t0
+    slo.use_reference_advance(False)
+    physics = "reference advance_board.c (oracle/_ref)" if slo.have_ref() else "oracle port"
+    return n_envs * steps / dt, dt, kind, physics
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = len(os.sched_getaffinity(0))
+    n_envs = ENVS_PER_GPU  # the same 4096-env batch; each step is one env-step of it
+    value, dt, kind, physics = cpu_arm(n_envs, args.steps, args.warmup, threads)
+    sample = "%d steps of %d append-still envs; physics = %s, rules = C port of safelife_game.py; %d threads" % (
+        args.steps, n_envs, physics, threads)
+    line = {
+        "impl": "reference", "metric": "env_steps_per_s", "value": value, "unit": "env-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+        "config": {"workload": "append-still 26x26, 4096 lockstep envs, random actions, full env step"},
+        "cell_updates_per_s": value * 2 * H * W,
+        "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+
+    from safelife_k2_b200 import _lib, distributed
+    from safelife_k2_b200.safelife_env import SafeLifeEnv
+    from safelife_k2_b200.safelife_game import LevelPool
+
+    rank, world, local = distributed.init_from_env()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    n = ENVS_PER_GPU
+    lo = rank * n
+    lv = append_still_levels()
+    pool = LevelPool(lv, device=dev)
+    state_bytes = n * (2 * H * W * 2 + 64)
+    ring = max(4, int(np.ceil(2.2 * L2_BYTES / state_bytes)))
+    K, Wm = args.steps, max(3, args.warmup)
+
+    envs = []
+    for r in range(ring):
+        e = SafeLifeEnv(pool, num_envs=n, env_id0=lo + r * n * world, global_counter=None,
+                        compute_obs=False, auto_reset=True)
+        e.seed(0)
+        e.reset()
+        envs.append(e)
+    rng = np.random.RandomState(2 + rank)
+    n_act = 64
+    acts = torch.from_numpy(rng.randint(9, size=(n_act, n)).astype(np.uint8)).to(dev)
+    stats = torch.zeros(8, dtype=torch.int64, device=dev)
+    lib = _lib.load()
+    stream = torch.cuda.current_stream()
+
+    def step(i):
+        e = envs[i % ring]
+        g = e.game
+        _lib.check(lib.slb_env_step(pool.c, n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                                    acts[i % n_act].data_ptr(), 1000, 0, g.env_id0, e._reward.data_ptr(),
+                                    e._done.data_ptr(), e._stride(), stream.cuda_stream))
+
+    for i in range(Wm):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for i in range(Wm, Wm + K):
+        step(i)
+    e_last = envs[(Wm + K - 1) % ring]
+    _lib.check(lib.slb_accumulate_stats(n, e_last.game.state.data_ptr(), e_last._reward.data_ptr(),
+                                        e_last._done.data_ptr(), stats.data_ptr(), stream.cuda_stream))
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    launches = _lib.launch_count() - l0
+    ms = ev0.elapsed_time(ev1)
+    distributed.all_reduce_stats(stats)
+    if world > 1:
+        torch.distributed.barrier()
+    ms = distributed.max_over_ranks(ms, dev)
+    clocks = sampler.summary()
+
+    # ---- e2e: host-buffer step through the public API (pinned host actions in, reward/done out) ----
+    e2e_steps = min(K, 500)
+    h_act = torch.from_numpy(rng.randint(9, size=(n_act, n)).astype(np.uint8)).pin_memory()
+    h_rew = torch.zeros(n, dtype=torch.int32).pin_memory()
+    h_done = torch.zeros(n, dtype=torch.uint8).pin_memory()
+    for i in range(3):
+        envs[i % ring].step_host(h_act[i % n_act], h_rew, h_done)
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        envs[i % ring].step_host(h_act[i % n_act], h_rew, h_done)
+    torch.cuda.synchronize()
+    e2e_s = distributed.max_over_ranks(time.perf_counter() - t0, dev)
+
+    if rank != 0:
+        return
+    value = n * world * K / (ms * 1e-3)
+    peak, peak_src = load_peaks()
+    achieved = n * BYTES_PER_ENV_STEP / (ms * 1e-3 / K) / 1e9
+    line = {
+        "metric": "env_steps_per_s", "value": value, "unit": "env-steps/s", "n_gpus": world,
+        "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+        "config": {"workload": "append-still 26x26, 4096 lockstep envs per GPU, random actions, full env step "
+                               "(execute_action + advance_board x2 + reward + exit colours), k=1 step per launch",
+                   "envs_per_gpu": n, "board": [H, W], "l2": "ring of %d independent batches (%.0f MB state) > L2" % (
+                       ring, ring * state_bytes / 1e6)},
+        "cell_updates_per_s": value * 2 * H * W,
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "bytes_per_env_step": BYTES_PER_ENV_STEP, "kernel": "env step (per launch: 4096 envs)"},
+        "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": n,
+                "d2h_bytes_per_step": 5 * n, "steps": e2e_steps,
+                "what": "slb_env_step_host: pinned uint8 actions H2D, fused step, int32 reward + uint8 done D2H, sync"},
+        "stats_allreduce": distributed.stats_dict(stats),
+    }
+    # CPU baseline on this box's host cores, bounded sample (rank 0, N=1 only)
+    if world == 1 and not args.no_cpu:
+        threads = len(os.sched_getaffinity(0))
+        v, dt, kind, physics = cpu_arm(n, 10, 2, threads)
+        line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": threads, "kind": kind,
+                                "sample": "10 steps of the same 4096-env batch (%.1f s); physics = %s, rules = C port" % (dt, physics)}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        args.steps = args.steps if args.steps is not None else 20
+        args.warmup = args.warmup if args.warmup is not None else 2
+        run_reference(args)
+    else:
+        args.steps = args.steps if args.steps is not None else 2000
+        args.warmup = args.warmup if args.warmup is not None else 50
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

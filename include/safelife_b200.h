@@ -1,0 +1,177 @@
+/*
+ * safelife_b200.h — C ABI of libsafelife_b200.so: the B200 (sm_100a) batched SafeLife hot path.
+ *
+ * This is the drop-in boundary.  It replaces, for N lockstep boards on one GPU, what the reference
+ * binds through its CPython extension `safelife.speedups` (speedups_src/module.c:256-274) plus the
+ * Python rule code that sits directly on top of it on the hot path.  Every entry point is
+ * `extern "C"`, takes plain pointers/sizes (no torch types), launches asynchronously on the
+ * caller's CUDA stream (`stream` is a cudaStream_t passed as void*) and returns 0 on success or a
+ * negative slb_status; slb_last_error() gives the message (thread-local).  There is no CPU
+ * fallback anywhere behind this ABI.
+ *
+ * Pointers named d_* are DEVICE pointers; h_* are HOST pointers (the *_host entry points copy
+ * in/out themselves and are synchronous).
+ *
+ * Cell encoding (uint16, safelife/safelife_game.py:74-98, speedups_src/constants.h:4-25):
+ *   bit 0 alive, 1 agent, 2 pushable, 3 destructible, 4 frozen, 5 preserving, 6 inhibiting,
+ *   7 spawning, 8 exit, 9/10/11 colour r/g/b, 15 pullable (12-14 unused, passed through).
+ *
+ * Spawn randomness (replaces speedups_src/random.c:14-57): a counter-based stream.  Draw j of
+ * env e under seed s is Philox4x32-10(counter={j_lo,j_hi,e_lo,e_hi}, key={s_lo,s_hi});
+ * u53 = (x0>>5)<<26 | (x1>>6); the reference's `random_float() < spawn_prob`
+ * (advance_board.c:110, double < (double)float) is evaluated exactly as u53 < ceil(p_f32 * 2^53).
+ * Draws are consumed in raster order by eligible cells only, board before goals, exactly like the
+ * reference; the per-env draw counter is explicit state.
+ */
+#ifndef SAFELIFE_B200_H
+#define SAFELIFE_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SLB_ABI_VERSION 1
+
+typedef enum {
+    SLB_OK = 0,
+    SLB_ERR_INVALID = -1,     /* bad shape / argument (reference: SystemError/ValueError, module.c:29-32) */
+    SLB_ERR_CUDA = -2,        /* CUDA runtime error; message has cudaGetErrorString */
+    SLB_ERR_UNSUPPORTED = -3, /* size outside what the kernels support */
+    SLB_ERR_OVERFLOW = -4,    /* side-effect key table overflow */
+} slb_status;
+
+const char *slb_last_error(void);
+int slb_abi_version(void);
+/* number of kernels launched by this library in this process so far (bench `gpu_launches`) */
+uint64_t slb_launch_count(void);
+
+/* Per-env scalar state (replaces the GameState/SafeLifeEnv attributes listed in SURVEY.md A6/A12:
+ * safelife_game.py:155-168, safelife_env.py:162-175,190-195).  64 bytes, one per env. */
+typedef struct {
+    int32_t agent_x, agent_y;     /* GameState.agent_loc (x, y) */
+    int32_t orientation;          /* 0 up, 1 right, 2 down, 3 left */
+    int32_t game_over;            /* 0 / 1 */
+    int32_t num_steps;            /* SafeLifeGame.num_steps */
+    int32_t level_id;             /* index into the level pool */
+    int32_t episode_length;       /* SafeLifeEnv.episode_length */
+    int32_t episode_completed;    /* SafeLifeEnv.episode_completed */
+    int32_t old_points;           /* SafeLifeEnv._old_game_value */
+    int32_t can_exit;             /* can_exit() on the current board (kept fresh by reset/step) */
+    int32_t completed, possible;  /* last performance_ratio() */
+    int64_t episode_reward;       /* SafeLifeEnv.episode_reward */
+    uint64_t rng_counter;         /* next draw index of this env's stream */
+} slb_env_state;
+
+/* Level pool on the device (replaces _init_data of each game + the per-level scalars,
+ * safelife_game.py:184-212; file_finder.py:78-98 record layout). */
+typedef struct {
+    int32_t n_levels, h, w, words_per_row; /* words_per_row = (w + 31) / 32 */
+    const uint16_t *board;          /* [P,H,W] */
+    const uint16_t *goals;          /* [P,H,W] */
+    const int32_t *agent_x;         /* [P] */
+    const int32_t *agent_y;         /* [P] */
+    const int32_t *orientation;     /* [P] */
+    const float *spawn_prob;        /* [P] python float narrowed to C float (module.c:22-24) */
+    const double *min_performance;  /* [P] */
+    int32_t *baseline;              /* [P]   written by slb_pool_prepare */
+    uint32_t *exit_mask;            /* [P,H,words_per_row] written by slb_pool_prepare */
+} slb_pool;
+
+/* Fills pool->baseline (performance_ratio's baseline_score, safelife_game.py:622) and
+ * pool->exit_mask (update_exit_locs, :528-529). */
+int slb_pool_prepare(const slb_pool *pool, void *stream);
+
+/* ---- A1-A4: speedups.advance_board for N boards (module.c:19-44 -> advance_board.c:34-120) ----
+ * d_in/d_out: [N,H,W] uint16, d_in != d_out.  d_spawn_prob: [N] float.  Env ids are env_id0 + i.
+ * d_counters: [N] draw counters, read and advanced (NULL: start at 0, not written back).
+ * k_steps >= 1 steps are applied; d_in is never written.  d_scratch [N,H,W] is required only when
+ * k_steps > 1 and the board shape has no on-chip fast path (may be NULL otherwise). */
+int slb_advance_board(const uint16_t *d_in, uint16_t *d_out, int n, int h, int w,
+                      const float *d_spawn_prob, uint64_t seed, uint64_t env_id0,
+                      uint64_t *d_counters, int k_steps, uint16_t *d_scratch, void *stream);
+
+/* Same contract with HOST buffers (what `speedups.advance_board(ndarray, p)` binds): copies in,
+ * steps, copies out, synchronises.  h_counters may be NULL. */
+int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, int w,
+                           const float *h_spawn_prob, uint64_t seed, uint64_t env_id0,
+                           uint64_t *h_counters, int k_steps);
+
+/* ---- A17: reset (safelife_env.py:188-198; revert/deserialize safelife_game.py:196-212,229-234) --
+ * For every env i with d_mask == NULL or d_mask[i] != 0: load level d_level_ids[i]. */
+int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const uint8_t *d_mask,
+                  uint16_t *d_board, uint16_t *d_goals, slb_env_state *d_state, void *stream);
+
+/* ---- A7/A8: execute_action (safelife_game.py:347-393, move_agent :308-345) -----------------------
+ * d_actions: [N] uint8, 0 NULL, 1-4 MOVE U/R/D/L, 5-8 TOGGLE U/R/D/L (safelife_env.py:61-71).
+ * Uses and updates d_state (agent_x/y, orientation, game_over); can_exit is read from
+ * d_state[i].can_exit.  d_reward: [N] int32 action reward (0 / +1). */
+int slb_execute_action(uint16_t *d_board, int n, int h, int w, slb_env_state *d_state,
+                       const uint8_t *d_actions, int32_t *d_reward, void *stream);
+
+/* ---- A9-A11: current_points, performance_ratio, can_exit (safelife_game.py:590-631, 522-526) ----
+ * Any output pointer may be NULL.  Does not modify state. */
+int slb_points_and_performance(const slb_pool *pool, int n, const uint16_t *d_board,
+                               const uint16_t *d_goals, const slb_env_state *d_state,
+                               int32_t *d_points, int32_t *d_completed, int32_t *d_possible,
+                               uint8_t *d_can_exit, void *stream);
+
+/* update_exit_colors (safelife_game.py:531-537): evaluates can_exit() on the current board/goals,
+ * repaints the level's initial exit cells (272 / 784) and refreshes d_state[i].can_exit,
+ * .completed, .possible. */
+int slb_update_exit_colors(const slb_pool *pool, int n, uint16_t *d_board, const uint16_t *d_goals,
+                           slb_env_state *d_state, void *stream);
+
+/* ---- A12: one SafeLifeEnv.step for N envs, fused (safelife_env.py:157-186) ----------------------
+ * execute_action -> advance board -> advance goals -> current_points -> reward -> counters ->
+ * update_exit_colors -> done.  d_reward [N] int32, d_done [N] uint8 (either may be NULL).
+ * auto_reset_stride > 0: an env that finishes this step is reset (after its outputs are written)
+ * to level (level_id + auto_reset_stride) % n_levels. */
+int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+                 slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
+                 uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
+                 void *stream);
+
+/* T fused env-steps with pre-staged actions: d_actions [T,N] uint8, d_reward [T,N] int32,
+ * d_done [T,N] uint8 (outputs may be NULL).  Board state stays on chip between steps when the
+ * shape has a fast path; otherwise this loops slb_env_step. */
+int slb_env_rollout(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+                    slb_env_state *d_state, const uint8_t *d_actions, int t_steps, int time_limit,
+                    uint64_t seed, uint64_t env_id0, int32_t *d_reward, uint8_t *d_done,
+                    int auto_reset_stride, void *stream);
+
+/* Host-buffer step (the call a CPU-side policy makes): actions in, reward/done out, state stays
+ * resident on the device.  Synchronous. */
+int slb_env_step_host(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+                      slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
+                      uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
+                      int auto_reset_stride, void *stream);
+
+/* ---- A13/A14: side_effect_score up to the EMD (side_effects.py:59-141) ---------------------------
+ * For episode i: b0 = d_board0[i] advanced d_num_steps[i] times, then num_samples paired steps of
+ * b0 (inaction, draws first) and b1 = d_board1[i] (action); per-cell-type count maps.
+ * d_keys [N,kmax] uint16 (0 = empty slot), d_counts [N,2,kmax,H,W] uint16 (must be zeroed by the
+ * caller), d_nkeys [N] int32 (-1 on key-table overflow).  d_counters [N] in/out (may be NULL).
+ * d_scratch: [N,4,H,W] uint16 workspace, required only when 4*H*W*2 bytes exceed shared memory. */
+int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, int n, int h, int w,
+                           const int32_t *d_num_steps, int num_samples, const float *d_spawn_prob,
+                           uint64_t seed, uint64_t env_id0, uint64_t *d_counters, int kmax,
+                           uint16_t *d_keys, uint16_t *d_counts, int32_t *d_nkeys,
+                           uint16_t *d_scratch, void *stream);
+
+/* ---- statistics vector for the multi-GPU all-reduce -----------------------------
+ * d_stats[8] int64 += { sum reward, n done, sum episode_length of done envs, sum episode_reward of
+ * done envs, sum completed of done, sum possible of done, n envs stepped, n game_over }. */
+int slb_accumulate_stats(int n, const slb_env_state *d_state, const int32_t *d_reward,
+                         const uint8_t *d_done, int64_t *d_stats, void *stream);
+
+/* ---- "next" row 1: observation (safelife_env.py:125-155, helper_utils.py:41-74) ------------------
+ * d_obs: [N,vh,vw] uint16 words (bit b = channel b).  Channel split is a view-level bit test. */
+int slb_get_obs(const slb_pool *pool, int n, const uint16_t *d_board, const uint16_t *d_goals,
+                const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
+                uint16_t *d_obs, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -31,7 +31,7 @@ ENV_STATE_DTYPE = np.dtype(
         ("agent_x", "<i4"), ("agent_y", "<i4"), ("orientation", "<i4"), ("game_over", "<i4"),
         ("num_steps", "<i4"), ("level_id", "<i4"), ("episode_length", "<i4"),
         ("episode_completed", "<i4"),
-        ("old_points", "<i4"), ("can_exit", "<i4"), ("reserved0", "<i4"), ("reserved1", "<i4"),
+        ("old_points", "<i4"), ("can_exit", "<i4"), ("completed", "<i4"), ("possible", "<i4"),
         ("episode_reward", "<i8"), ("rng_counter", "<u8"),
     ]
 )

@@ -44,7 +44,7 @@ void slo_advance_board(const uint16_t *in, uint16_t *out, int h, int w, float sp
 typedef struct {
     int32_t agent_x, agent_y, orientation, game_over;
     int32_t num_steps, level_id, episode_length, episode_completed;
-    int32_t old_points, can_exit, reserved0, reserved1;
+    int32_t old_points, can_exit, completed, possible;
     int64_t episode_reward;
     uint64_t rng_counter;
 } slo_env_state; /* 64 bytes */

@@ -1,0 +1,367 @@
+// slb_api.cu — the C ABI of libsafelife_b200.so (include/safelife_b200.h): argument checks, kernel
+// selection (bit-sliced fast path vs shape-generic path) and launches.  No CPU fallback.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "slb_fast.cuh"
+#include "slb_generic_env.cuh"
+
+using namespace slb;
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define SLB_CUDA(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t e_ = (expr);                                                             \
+        if (e_ != cudaSuccess)                                                               \
+            return fail(SLB_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));       \
+    } while (0)
+
+#define SLB_LAUNCHED()                                                                       \
+    do {                                                                                     \
+        g_launches.fetch_add(1, std::memory_order_relaxed);                                  \
+        cudaError_t e_ = cudaGetLastError();                                                 \
+        if (e_ != cudaSuccess)                                                               \
+            return fail(SLB_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e_));   \
+    } while (0)
+
+int check_shape(int n, int h, int w) {
+    if (n < 0) return fail(SLB_ERR_INVALID, "n must be >= 0 (got %d)", n);
+    if (h < 3 || w < 3)
+        return fail(SLB_ERR_INVALID,
+                    "board must be at least 3x3 (got %dx%d): the reference double-counts wrapped "
+                    "neighbours below that (SURVEY.md Appendix A)", h, w);
+    if ((long long)h * w > (1ll << 28)) return fail(SLB_ERR_UNSUPPORTED, "board too large");
+    return 0;
+}
+
+int check_pool(const slb_pool *p) {
+    if (!p) return fail(SLB_ERR_INVALID, "pool is NULL");
+    if (p->n_levels <= 0) return fail(SLB_ERR_INVALID, "pool has no levels");
+    if (p->words_per_row != (p->w + 31) / 32) return fail(SLB_ERR_INVALID, "pool.words_per_row");
+    if (!p->board || !p->goals || !p->agent_x || !p->agent_y || !p->orientation ||
+        !p->spawn_prob || !p->min_performance || !p->baseline || !p->exit_mask)
+        return fail(SLB_ERR_INVALID, "pool has NULL arrays");
+    return check_shape(0, p->h, p->w);
+}
+
+constexpr size_t kSmemStatic = 2048;  // static shared memory of the generic kernels (upper bound)
+size_t g_smem_optin = 0;
+
+size_t smem_optin() {
+    if (!g_smem_optin) {
+        int dev = 0, v = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        g_smem_optin = (size_t)v;
+    }
+    return g_smem_optin;
+}
+
+template <typename K>
+int allow_smem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024)
+        SLB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *slb_last_error(void) { return g_err; }
+int slb_abi_version(void) { return SLB_ABI_VERSION; }
+uint64_t slb_launch_count(void) { return g_launches.load(); }
+
+int slb_pool_prepare(const slb_pool *pool, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    pool_prepare_kernel<<<pool->n_levels, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+static int advance_once(const uint16_t *in, uint16_t *out, int n, int h, int w, const float *p,
+                        uint64_t seed, uint64_t env0, uint64_t *ctr, cudaStream_t st) {
+    if (fast_shape(h, w)) {
+        launch_advance_fast(in, out, n, h, w, p, seed, env0, ctr, 1, st);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    size_t bytes = (size_t)h * w * 2;
+    if (bytes + kSmemStatic <= smem_optin()) {
+        if (int rc = allow_smem(advance_generic_kernel<true>, bytes)) return rc;
+        advance_generic_kernel<true><<<n, GEN_THREADS, bytes, st>>>(in, out, h, w, p, seed, env0, ctr);
+    } else {
+        advance_generic_kernel<false><<<n, GEN_THREADS, 0, st>>>(in, out, h, w, p, seed, env0, ctr);
+    }
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_advance_board(const uint16_t *d_in, uint16_t *d_out, int n, int h, int w,
+                      const float *d_spawn_prob, uint64_t seed, uint64_t env_id0,
+                      uint64_t *d_counters, int k_steps, uint16_t *d_scratch, void *stream) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!d_in || !d_out || !d_spawn_prob) return fail(SLB_ERR_INVALID, "NULL board/spawn_prob pointer");
+    if (d_in == d_out) return fail(SLB_ERR_INVALID, "advance_board is out of place: d_in == d_out");
+    if (k_steps < 1) return fail(SLB_ERR_INVALID, "k_steps must be >= 1");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fast_shape(h, w)) {  // k steps on chip, one HBM round trip
+        launch_advance_fast(d_in, d_out, n, h, w, d_spawn_prob, seed, env_id0, d_counters, k_steps, st);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    if (k_steps > 1 && !d_scratch)
+        return fail(SLB_ERR_INVALID, "k_steps > 1 on a %dx%d board needs d_scratch", h, w);
+    // ping-pong so that the last step lands in d_out
+    const uint16_t *src = d_in;
+    for (int k = 0; k < k_steps; k++) {
+        uint16_t *dst = ((k_steps - 1 - k) % 2 == 0) ? d_out : d_scratch;
+        if (int rc = advance_once(src, dst, n, h, w, d_spawn_prob, seed, env_id0, d_counters, st)) return rc;
+        src = dst;
+    }
+    return SLB_OK;
+}
+
+int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, int w,
+                           const float *h_spawn_prob, uint64_t seed, uint64_t env_id0,
+                           uint64_t *h_counters, int k_steps) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!h_in || !h_out || !h_spawn_prob) return fail(SLB_ERR_INVALID, "NULL host pointer");
+    if (n == 0) return SLB_OK;
+    size_t cells = (size_t)n * h * w;
+    uint16_t *d_buf = nullptr;
+    float *d_p = nullptr;
+    uint64_t *d_c = nullptr;
+    cudaStream_t st = nullptr;
+    int rc = SLB_OK;
+    bool need_scratch = k_steps > 1 && !fast_shape(h, w);
+    SLB_CUDA(cudaMalloc(&d_buf, cells * 2 * (need_scratch ? 3 : 2)));
+    if (cudaMalloc(&d_p, (size_t)n * 4) != cudaSuccess || cudaMalloc(&d_c, (size_t)n * 8) != cudaSuccess) {
+        rc = fail(SLB_ERR_CUDA, "cudaMalloc failed");
+    } else {
+        cudaMemcpyAsync(d_buf, h_in, cells * 2, cudaMemcpyHostToDevice, st);
+        cudaMemcpyAsync(d_p, h_spawn_prob, (size_t)n * 4, cudaMemcpyHostToDevice, st);
+        if (h_counters) cudaMemcpyAsync(d_c, h_counters, (size_t)n * 8, cudaMemcpyHostToDevice, st);
+        else cudaMemsetAsync(d_c, 0, (size_t)n * 8, st);
+        rc = slb_advance_board(d_buf, d_buf + cells, n, h, w, d_p, seed, env_id0, d_c, k_steps,
+                               need_scratch ? d_buf + 2 * cells : nullptr, st);
+        if (rc == SLB_OK) {
+            cudaMemcpyAsync(h_out, d_buf + cells, cells * 2, cudaMemcpyDeviceToHost, st);
+            if (h_counters) cudaMemcpyAsync(h_counters, d_c, (size_t)n * 8, cudaMemcpyDeviceToHost, st);
+            cudaError_t e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) rc = fail(SLB_ERR_CUDA, "advance_board_host: %s", cudaGetErrorString(e));
+        }
+    }
+    cudaFree(d_buf);
+    cudaFree(d_p);
+    cudaFree(d_c);
+    return rc;
+}
+
+int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const uint8_t *d_mask,
+                  uint16_t *d_board, uint16_t *d_goals, slb_env_state *d_state, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_level_ids || !d_board || !d_goals || !d_state)
+        return fail(SLB_ERR_INVALID, "slb_env_reset: bad arguments");
+    if (n == 0) return SLB_OK;
+    reset_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool, d_level_ids, d_mask,
+                                                                      d_board, d_goals, d_state);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_execute_action(uint16_t *d_board, int n, int h, int w, slb_env_state *d_state,
+                       const uint8_t *d_actions, int32_t *d_reward, void *stream) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!d_board || !d_state || !d_actions) return fail(SLB_ERR_INVALID, "slb_execute_action: NULL pointer");
+    if (n == 0) return SLB_OK;
+    execute_action_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(d_board, n, h, w, d_state,
+                                                                           d_actions, d_reward);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_points_and_performance(const slb_pool *pool, int n, const uint16_t *d_board,
+                               const uint16_t *d_goals, const slb_env_state *d_state,
+                               int32_t *d_points, int32_t *d_completed, int32_t *d_possible,
+                               uint8_t *d_can_exit, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_board || !d_goals || !d_state) return fail(SLB_ERR_INVALID, "slb_points: bad arguments");
+    if (n == 0) return SLB_OK;
+    points_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
+        *pool, d_board, d_goals, d_state, d_points, d_completed, d_possible, d_can_exit);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_update_exit_colors(const slb_pool *pool, int n, uint16_t *d_board, const uint16_t *d_goals,
+                           slb_env_state *d_state, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_board || !d_goals || !d_state)
+        return fail(SLB_ERR_INVALID, "slb_update_exit_colors: bad arguments");
+    if (n == 0) return SLB_OK;
+    exit_colors_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool, d_board, d_goals, d_state);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+                 slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
+                 uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
+                 void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_board || !d_goals || !d_state || !d_actions)
+        return fail(SLB_ERR_INVALID, "slb_env_step: bad arguments");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fast_shape(pool->h, pool->w)) {
+        launch_env_rollout_fast(*pool, n, d_board, d_goals, d_state, d_actions, 1, time_limit, seed,
+                                env_id0, d_reward, d_done, auto_reset_stride, st);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    size_t bytes = (size_t)pool->h * pool->w * 2;
+    if (bytes + kSmemStatic > smem_optin())
+        return fail(SLB_ERR_UNSUPPORTED, "fused env step needs the %dx%d board in shared memory",
+                    pool->h, pool->w);
+    if (int rc = allow_smem(env_step_generic_kernel, bytes)) return rc;
+    env_step_generic_kernel<<<n, GEN_THREADS, bytes, st>>>(*pool, d_board, d_goals, d_state, d_actions,
+                                                          time_limit, seed, env_id0, d_reward,
+                                                          d_done, auto_reset_stride);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_env_rollout(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+                    slb_env_state *d_state, const uint8_t *d_actions, int t_steps, int time_limit,
+                    uint64_t seed, uint64_t env_id0, int32_t *d_reward, uint8_t *d_done,
+                    int auto_reset_stride, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || t_steps < 0 || !d_board || !d_goals || !d_state || !d_actions)
+        return fail(SLB_ERR_INVALID, "slb_env_rollout: bad arguments");
+    if (n == 0 || t_steps == 0) return SLB_OK;
+    if (fast_shape(pool->h, pool->w)) {
+        launch_env_rollout_fast(*pool, n, d_board, d_goals, d_state, d_actions, t_steps, time_limit,
+                                seed, env_id0, d_reward, d_done, auto_reset_stride,
+                                (cudaStream_t)stream);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    for (int t = 0; t < t_steps; t++) {
+        int rc = slb_env_step(pool, n, d_board, d_goals, d_state, d_actions + (size_t)t * n, time_limit,
+                              seed, env_id0, d_reward ? d_reward + (size_t)t * n : nullptr,
+                              d_done ? d_done + (size_t)t * n : nullptr, auto_reset_stride, stream);
+        if (rc) return rc;
+    }
+    return SLB_OK;
+}
+
+
+int slb_env_step_host(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+                      slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
+                      uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
+                      int auto_reset_stride, void *stream) {
+    if (n < 0 || !h_actions) return fail(SLB_ERR_INVALID, "slb_env_step_host: bad arguments");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    // one staging block per calling thread, grown on demand: [actions n | done n | pad | reward 4n]
+    thread_local uint8_t *d_io = nullptr;
+    thread_local size_t d_io_cap = 0;
+    size_t off_done = (size_t)n, off_rew = ((size_t)2 * n + 15) & ~(size_t)15;
+    size_t need = off_rew + (size_t)4 * n;
+    if (need > d_io_cap) {
+        if (d_io) cudaFree(d_io);
+        d_io = nullptr;
+        d_io_cap = 0;
+        SLB_CUDA(cudaMalloc(&d_io, need));
+        d_io_cap = need;
+    }
+    SLB_CUDA(cudaMemcpyAsync(d_io, h_actions, (size_t)n, cudaMemcpyHostToDevice, st));
+    int rc = slb_env_step(pool, n, d_board, d_goals, d_state, d_io, time_limit, seed, env_id0,
+                          (int32_t *)(d_io + off_rew), d_io + off_done, auto_reset_stride, stream);
+    if (rc) return rc;
+    if (h_done) SLB_CUDA(cudaMemcpyAsync(h_done, d_io + off_done, (size_t)n, cudaMemcpyDeviceToHost, st));
+    if (h_reward)
+        SLB_CUDA(cudaMemcpyAsync(h_reward, d_io + off_rew, (size_t)4 * n, cudaMemcpyDeviceToHost, st));
+    SLB_CUDA(cudaStreamSynchronize(st));
+    return SLB_OK;
+}
+
+int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, int n, int h, int w,
+                           const int32_t *d_num_steps, int num_samples, const float *d_spawn_prob,
+                           uint64_t seed, uint64_t env_id0, uint64_t *d_counters, int kmax,
+                           uint16_t *d_keys, uint16_t *d_counts, int32_t *d_nkeys,
+                           uint16_t *d_scratch, void *stream) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!d_board0 || !d_board1 || !d_num_steps || !d_spawn_prob || !d_keys || !d_counts || !d_nkeys)
+        return fail(SLB_ERR_INVALID, "slb_side_effect_counts: NULL pointer");
+    if (kmax < 1 || kmax > SE_MAX_KEYS)
+        return fail(SLB_ERR_INVALID, "kmax must be in [1, %d]", SE_MAX_KEYS);
+    if (num_samples < 0 || num_samples > 65535)
+        return fail(SLB_ERR_INVALID, "num_samples must fit the uint16 count maps (<= 65535)");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fast_shape(h, w)) {
+        launch_side_effect_fast(d_board0, d_board1, n, h, w, d_num_steps, num_samples, d_spawn_prob,
+                                seed, env_id0, d_counters, kmax, d_keys, d_counts, d_nkeys, st);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    size_t bytes = (size_t)4 * h * w * 2;
+    if (bytes + kSmemStatic <= smem_optin()) {
+        if (int rc = allow_smem(side_effect_generic_kernel<true>, bytes)) return rc;
+        side_effect_generic_kernel<true><<<n, GEN_THREADS, bytes, st>>>(
+            d_board0, d_board1, h, w, d_num_steps, num_samples, d_spawn_prob, seed, env_id0,
+            d_counters, kmax, d_keys, d_counts, d_nkeys, nullptr);
+    } else {
+        if (!d_scratch)
+            return fail(SLB_ERR_INVALID, "%dx%d boards need d_scratch [N,4,H,W] for side effects", h, w);
+        side_effect_generic_kernel<false><<<n, GEN_THREADS, 0, st>>>(
+            d_board0, d_board1, h, w, d_num_steps, num_samples, d_spawn_prob, seed, env_id0,
+            d_counters, kmax, d_keys, d_counts, d_nkeys, d_scratch);
+    }
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_accumulate_stats(int n, const slb_env_state *d_state, const int32_t *d_reward,
+                         const uint8_t *d_done, int64_t *d_stats, void *stream) {
+    if (n < 0 || !d_state || !d_stats) return fail(SLB_ERR_INVALID, "slb_accumulate_stats: bad arguments");
+    if (n == 0) return SLB_OK;
+    int blocks = (n + 255) / 256;
+    if (blocks > 148) blocks = 148;
+    stats_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(n, d_state, d_reward, d_done,
+                                                          (unsigned long long *)d_stats);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_get_obs(const slb_pool *pool, int n, const uint16_t *d_board, const uint16_t *d_goals,
+                const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
+                uint16_t *d_obs, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || vh < 1 || vw < 1 || !d_board || !d_goals || !d_state || !d_obs)
+        return fail(SLB_ERR_INVALID, "slb_get_obs: bad arguments");
+    if (n == 0) return SLB_OK;
+    get_obs_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool, d_board, d_goals, d_state, vh, vw,
+                                                               remove_white_goals, d_obs);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,161 @@
+"""
+Batched SafeLifeEnv — host-side mirror of the reference's ``safelife/safelife_env.py`` (old-gym
+API: reset() -> obs, step(a) -> (obs, reward, done, info), seed(s) -> [s]) for N lockstep
+environments on one B200.  One fused CUDA launch per step (slb_env_step) does
+execute_action -> advance_board (board, goals) -> current_points -> reward -> update_exit_colors
+-> done for every env (safelife_env.py:157-186); observations come from slb_get_obs
+(safelife_env.py:125-155).
+
+Keyword parameters keep the reference names: time_limit, remove_white_goals, view_shape,
+output_channels, global_counter (safelife_env.py:73-95).
+"""
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+from . import _lib
+from .safelife_game import ACTION_NAMES, LevelPool, SafeLifeGame
+
+
+class SafeLifeEnv(object):
+    metadata = {"render.modes": []}
+    action_names = ACTION_NAMES
+    game = None
+
+    time_limit = 1000
+    remove_white_goals = True
+    view_shape = (15, 15)
+    output_channels = tuple(range(15))
+    global_counter = SimpleNamespace(episodes_started=0, episodes_completed=0, num_steps=0)
+
+    # batched-only knobs
+    num_envs = 1
+    env_id0 = 0          # global index of this shard's first env (placement-independent streams)
+    auto_reset = False   # reset finished envs inside the step kernel (ContinuingEnv-like)
+    compute_obs = True   # False: step()/reset() return obs=None (policy reads game.board itself)
+
+    def __init__(self, level_iterator, **kwargs):
+        """level_iterator: a LevelPool, or anything LevelPool accepts (structured level array,
+        list of level records).  Env i plays levels i, i+N, i+2N, ... (mod pool size)."""
+        for key, val in kwargs.items():
+            if not key.startswith("_") and hasattr(self, key) and not callable(getattr(self, key)):
+                setattr(self, key, val)
+            else:
+                raise ValueError("Unrecognized parameter: '%s'" % (key,))
+        self.pool = level_iterator if isinstance(level_iterator, LevelPool) else LevelPool(level_iterator)
+        self.num_envs = int(self.num_envs)
+        self._seed = 0
+        self._lib = _lib.load()
+        dev = self.pool.device
+        self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
+        self._done = torch.zeros(self.num_envs, dtype=torch.uint8, device=dev)
+        self._next_level = (np.arange(self.num_envs) + self.env_id0) % self.pool.n_levels
+        self.seed()
+
+    # ------------------------------------------------------------------------------------------
+    def seed(self, seed=None):
+        """safelife_env.py:120-123: sets the seed of the spawn streams (the reference reseeds the
+        global numpy stream through speedups.seed).  Draw counters restart at the next reset()."""
+        if seed is None:
+            seed = int(np.random.SeedSequence().generate_state(1)[0] & 0x7FFFFFFF)
+        self._seed = int(seed)
+        if self.game is not None:
+            self.game.seed = self._seed
+            self.game.rng_counter.zero_()
+        return [seed]
+
+    def _stride(self):
+        return self.num_envs % self.pool.n_levels if self.num_envs % self.pool.n_levels else self.pool.n_levels
+
+    def reset(self, mask=None):
+        """safelife_env.py:188-198 for every env (or the envs selected by `mask`)."""
+        if self.game is None:
+            self.game = SafeLifeGame(self.pool, self.num_envs, seed=self._seed, env_id0=self.env_id0,
+                                     level_ids=self._next_level)
+            started = self.num_envs
+            self._next_level = (self._next_level + self.num_envs) % self.pool.n_levels
+        else:
+            m = np.ones(self.num_envs, bool) if mask is None else np.asarray(
+                mask.cpu() if hasattr(mask, "cpu") else mask).astype(bool)
+            self.game.revert(self._next_level, mask=m)
+            self._next_level = np.where(m, (self._next_level + self.num_envs) % self.pool.n_levels,
+                                        self._next_level)
+            started = int(m.sum())
+        if self.global_counter is not None:
+            self.global_counter.episodes_started += started
+        return self.get_obs() if self.compute_obs else None
+
+    def get_obs(self):
+        """uint16 [N,vh,vw,C] (output_channels) or [N,vh,vw] (output_channels None)."""
+        g = self.game
+        vh, vw = self.view_shape
+        words = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=self.pool.device)
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_get_obs(self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(),
+                                             g.state.data_ptr(), vh, vw, int(self.remove_white_goals),
+                                             words.data_ptr(), _lib.current_stream()))
+        if not self.output_channels:
+            return words
+        shift = torch.tensor(list(self.output_channels), dtype=torch.int32, device=self.pool.device)
+        bits = (words.to(torch.int32)[..., None] >> shift) & 1
+        return bits.to(torch.uint16)
+
+    def step(self, action):
+        """action: int array/tensor [N] (0..8).  Returns (obs, reward int32 [N], done bool [N], info)."""
+        assert self.game is not None, "Game state is not initialized."
+        g = self.game
+        acts = g._actions(action)
+        already = g._field("episode_completed").clone() if self.global_counter is not None else None
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_env_step(
+                self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
+                self._done.data_ptr(), self._stride() if self.auto_reset else 0,
+                _lib.current_stream()))
+        done = self._done != 0
+        if self.global_counter is not None:
+            fresh = already == 0
+            self.global_counter.episodes_completed += int((done & fresh).sum().item())
+            self.global_counter.num_steps += int(fresh.sum().item())
+        info = {
+            "board": g.board, "goals": g.goals, "agent_loc": g.agent_loc,
+            "times_up": g._field("episode_length") > self.time_limit,
+            "episode": {"length": g._field("episode_length"), "reward": g._field("episode_reward")},
+        }
+        return (self.get_obs() if self.compute_obs else None), self._reward, done, info
+
+    def step_host(self, actions_host, reward_host, done_host):
+        """Host-buffer step through slb_env_step_host: uint8 actions in (pinned) host memory in,
+        int32 rewards / uint8 dones out; board state stays resident on the device.  Synchronous."""
+        g = self.game
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_env_step_host(
+                self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                _lib.ptr(actions_host), int(self.time_limit), g.seed, g.env_id0,
+                _lib.ptr(reward_host), _lib.ptr(done_host),
+                self._stride() if self.auto_reset else 0, _lib.current_stream()))
+
+    def rollout(self, actions, reward=None, done=None):
+        """T fused steps with pre-staged actions: uint8 [T,N] cuda tensor.  Returns (reward int32
+        [T,N], done uint8 [T,N]).  Board state stays on chip between steps on fast-path shapes."""
+        g = self.game
+        T = actions.shape[0]
+        dev = self.pool.device
+        if reward is None:
+            reward = torch.empty((T, g.n), dtype=torch.int32, device=dev)
+        if done is None:
+            done = torch.empty((T, g.n), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(self._lib.slb_env_rollout(
+                self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                actions.data_ptr(), int(T), int(self.time_limit), g.seed, g.env_id0,
+                reward.data_ptr(), done.data_ptr(), self._stride() if self.auto_reset else 0,
+                _lib.current_stream()))
+        return reward, done
+
+    def render(self, mode="ansi"):
+        raise NotImplementedError("rendering is out of scope (SURVEY.md §2.1)")
+
+    def close(self):
+        pass

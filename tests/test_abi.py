@@ -1,0 +1,66 @@
+"""CPU: the C-ABI library loads and exports every symbol include/safelife_b200.h declares; the
+argument checks that run before any CUDA call behave; the product never imports the oracle."""
+import ctypes
+import os
+import re
+
+from tests.conftest import ROOT
+
+HEADER = os.path.join(ROOT, "include", "safelife_b200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(slb_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from safelife_k2_b200 import _lib
+
+    names = declared_symbols()
+    assert len(names) >= 16
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), "libsafelife_b200.so does not export %s" % n
+    assert sorted(_lib.SYMBOLS) == names, "python binding table out of sync with the header"
+    assert _lib.load().slb_abi_version() == 1
+
+
+def test_env_state_layout_matches_header():
+    from safelife_k2_b200.safelife_game import ENV_STATE_DTYPE
+    from oracle.slo import ENV_STATE_DTYPE as ORACLE_DTYPE
+
+    src = open(HEADER).read()
+    body = src[src.index("typedef struct {", src.index("Per-env scalar state")):src.index("} slb_env_state;")]
+    fields = []
+    for ctype, names in re.findall(r"\b(int32_t|int64_t|uint64_t)\s+([a-z_, ]+);", body):
+        fields += [n.strip() for n in names.split(",")]
+    assert fields == list(ENV_STATE_DTYPE.names) == list(ORACLE_DTYPE.names)
+    assert ENV_STATE_DTYPE.itemsize == 64
+
+
+def test_argument_checks_without_gpu():
+    from safelife_k2_b200 import _lib
+
+    L = _lib.load()
+    one = ctypes.create_string_buffer(64)
+    a = ctypes.addressof(one)
+    assert L.slb_advance_board(a, a + 32, 1, 2, 5, a, 0, 0, None, 1, None, None) == _lib.SLB_ERR_INVALID
+    assert b"3x3" in L.slb_last_error()
+    assert L.slb_advance_board(a, a, 1, 4, 4, a, 0, 0, None, 1, None, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_advance_board(a, a + 32, 1, 4, 4, a, 0, 0, None, 0, None, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_advance_board(None, a, 1, 4, 4, a, 0, 0, None, 1, None, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_pool_prepare(None, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_side_effect_counts(a, a, 1, 4, 4, a, 10, a, 0, 0, None, 1000, a, a, a, None, None) \
+        == _lib.SLB_ERR_INVALID
+
+
+def test_product_does_not_touch_the_oracle():
+    pkg = os.path.join(ROOT, "safelife_k2_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.replace("parity oracle", ""), f
+                assert "slo_" not in text, f

@@ -1,0 +1,263 @@
+"""GPU parity tests: the CUDA path (through the C ABI / the host mirror of the reference interface)
+against the golden vectors generated from the reference and against the CPU oracle on the same
+seeded inputs.  Bit-exact: this is integer / byte work."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import slo
+from tests import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sl():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from safelife_k2_b200 import _lib, safelife_env, safelife_game, side_effects, speedups
+
+    _lib.load()  # fails loudly if the CUDA library is missing
+    return type("M", (), dict(lib=_lib, env=safelife_env, game=safelife_game, se=side_effects,
+                              speedups=speedups))
+
+
+def dev_advance(sl, boards, p, seed, env0, counters=None, k=1):
+    """boards: numpy [N,H,W] -> (numpy out, counters) through slb_advance_board on the device."""
+    b = torch.from_numpy(np.ascontiguousarray(boards, dtype=np.uint16)).cuda()
+    n, h, w = b.shape
+    out = torch.empty_like(b)
+    pp = torch.full((n,), float(np.float32(p)), dtype=torch.float32, device="cuda")
+    ctr = torch.zeros(n, dtype=torch.int64, device="cuda")
+    if counters is not None:
+        ctr.copy_(torch.from_numpy(np.asarray(counters, dtype=np.int64)))
+    scratch = torch.empty_like(b) if k > 1 else None
+    sl.lib.check(sl.lib.load().slb_advance_board(b.data_ptr(), out.data_ptr(), n, h, w, pp.data_ptr(),
+                                                 seed, env0, ctr.data_ptr(), k,
+                                                 sl.lib.ptr(scratch), sl.lib.current_stream()))
+    torch.cuda.synchronize()
+    return out.cpu().numpy(), ctr.cpu().numpy()
+
+
+def test_advance_board_known_answers(sl):
+    n = 0
+    for name, env, seed, board, outs, p in gu.kat_cases():
+        b, ctr = board[None], None
+        for t in range(outs.shape[0]):
+            b, ctr = dev_advance(sl, b, p, seed, env, ctr)
+            assert (b[0] == outs[t]).all(), "%s step %d" % (name, t)
+        # k fused steps give the same final board and counter
+        bk, ctrk = dev_advance(sl, board[None], p, seed, env, None, k=outs.shape[0])
+        assert (bk[0] == outs[-1]).all() and ctrk[0] == ctr[0], name
+        n += 1
+    assert n > 80
+
+
+def test_speedups_module_contract(sl):
+    sp = sl.speedups
+    b = np.zeros((7, 7), np.uint16)
+    b[3, 2:5] = 9 | 512
+    out = sp.advance_board(b)
+    assert out.dtype == np.uint16 and out.shape == (7, 7) and out is not b
+    assert (b[3, 2:5] == 521).all()  # input not mutated
+    assert (out[2:5, 3] == 521).all() and out.sum() == 3 * 521
+    # list / int64 input is force-cast like NPY_ARRAY_FORCECAST
+    assert (sp.advance_board(b.astype(np.int64).tolist()) == out).all()
+    with pytest.raises(ValueError):
+        sp.advance_board(np.zeros((0, 5), np.uint16))
+    with pytest.raises(ValueError):
+        sp.advance_board(np.zeros(5, np.uint16))
+    with pytest.raises(sl.lib.SlbError):
+        sp.advance_board(np.zeros((2, 5), np.uint16))
+    # stochastic: module stream, seed() rewinds
+    s = np.zeros((5, 5), np.uint16)
+    s[2, 2] = 16 | 128 | 8 | 1024
+    sp.seed(5)
+    a1 = sp.advance_board(s, 0.3)
+    a2 = sp.advance_board(a1, 0.3)
+    sp.seed(5)
+    assert (sp.advance_board(s, 0.3) == a1).all()
+    o1, c1 = slo.advance_board(s, 0.3, seed=5, env=0, counter=0)
+    o2, _ = slo.advance_board(o1, 0.3, seed=5, env=0, counter=c1)
+    assert (a1 == o1).all() and (a2 == o2).all()
+    # CUDA tensor in -> CUDA tensor out
+    t = torch.from_numpy(b).cuda()
+    assert (sp.advance_board(t).cpu().numpy() == out).all()
+
+
+@pytest.mark.parametrize("archive", ["append_still", "prune_spawn", "append_spawn", "navigation"])
+def test_env_trace(sl, archive):
+    tr = gu.load("trace_%s.npz" % archive)
+    lv = gu.levels(str(tr["archive"]))
+    l0 = int(tr["level0"])
+    pool = sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 2))
+    env = sl.env.SafeLifeEnv(pool, num_envs=1, env_id0=int(tr["env_id"]), global_counter=None,
+                             compute_obs=False)
+    env.seed(int(tr["seed"]))
+    env.reset()
+    for t, a in enumerate(tr["actions"]):
+        _, r, d, info = env.step(np.array([a]))
+        st = env.game.state_numpy()[0]
+        assert (info["board"][0].cpu().numpy() == tr["board"][t]).all(), t
+        assert (info["goals"][0].cpu().numpy() == tr["goals"][t]).all(), t
+        assert int(r[0]) == tr["reward"][t] and bool(d[0]) == bool(tr["done"][t]), t
+        assert bool(info["times_up"][0]) == bool(tr["times_up"][t])
+        assert (st["agent_x"], st["agent_y"]) == tuple(tr["agent_loc"][t])
+        assert st["orientation"] == tr["orientation"][t]
+        assert st["old_points"] == tr["points"][t]
+        assert st["completed"] == tr["completed"][t] and st["possible"] == tr["possible"][t]
+        if d[0]:
+            env.reset()
+
+
+def test_scenarios(sl):
+    d = gu.load("scenarios.npz")
+    for i, name in enumerate(d["names"]):
+        rec = {"board": d["board0_%d" % i][None], "goals": d["goals0_%d" % i][None],
+               "agent_loc": d["agent_%d" % i][None, :2], "orientation": d["agent_%d" % i][None, 2],
+               "spawn_prob": np.array([0.3]), "min_performance": d["minperf_%d" % i][None]}
+        pool = sl.game.LevelPool(rec)
+        g = sl.game.SafeLifeGame(pool, 1, seed=int(d["seed"]), env_id0=1000 + i)
+        assert (g.board[0].cpu().numpy() == d["start_%d" % i]).all(), name
+        for t, a in enumerate(d["actions_%d" % i]):
+            meta = d["meta_%d" % i][t]
+            assert bool(g.can_exit()[0]) == bool(meta[5]), (name, t)
+            r = g.execute_action(sl.game.ACTION_NAMES[int(a)])
+            assert (g.board[0].cpu().numpy() == d["boards_%d" % i][t, 0]).all(), (name, t)
+            st = g.state_numpy()[0]
+            assert (int(r[0]), st["agent_x"], st["agent_y"], st["orientation"], st["game_over"]) == \
+                tuple(int(v) for v in meta[:5]), (name, t)
+            g.advance_board()
+            assert int(g.current_points()[0]) == meta[6]
+            assert int(g.performance_ratio()[0][0]) == meta[7]
+            g.update_exit_colors()
+            assert (g.board[0].cpu().numpy() == d["boards_%d" % i][t, 1]).all(), (name, t)
+            assert (g.goals[0].cpu().numpy() == d["goals_%d" % i][t]).all(), (name, t)
+
+
+def test_side_effect_counts_golden(sl):
+    d = gu.load("side_effects.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        pool = sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 1))
+        env = sl.env.SafeLifeEnv(pool, num_envs=1, env_id0=int(d["env_%d" % i]), global_counter=None,
+                                 compute_obs=False)
+        env.seed(int(d["seed"]))
+        env.reset()
+        for a in d["actions_%d" % i]:
+            env.step(np.array([a]))
+        assert (env.game.board[0].cpu().numpy() == d["final_board_%d" % i]).all()
+        n = int(d["num_samples_%d" % i])
+        res = sl.se.side_effect_score(env.game, num_samples=n, emd=False)[0]
+        keys = sorted(int(k) for k in res)
+        assert keys == d["keys_%d" % i].tolist()
+        assert [res[np.uint16(k)][1] for k in keys] == d["sum_inaction_%d" % i].tolist()
+
+
+def _oracle_vs_device(sl, archive, n, steps, seed, aseed, auto_reset, check_every=25):
+    lv = gu.levels(archive)
+    pool = sl.game.LevelPool(lv)
+    opool = slo.OraclePool(**lv)
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=77, global_counter=None, compute_obs=False,
+                             auto_reset=auto_reset, time_limit=60 if auto_reset else 1000)
+    env.seed(seed)
+    env.reset()
+    lvl = (np.arange(n) + 77) % pool.n_levels
+    oenv = slo.OracleBatchEnv(opool, lvl, seed=seed, env_id0=77, threads=8,
+                              time_limit=60 if auto_reset else 1000)
+    rng = np.random.RandomState(aseed)
+    stride = n % pool.n_levels or pool.n_levels
+    for t in range(steps):
+        acts = rng.randint(9, size=n)
+        _, r, d, _ = env.step(acts)
+        orr, od = oenv.step(acts)
+        assert (r.cpu().numpy() == orr).all(), t
+        assert (d.cpu().numpy() == (od != 0)).all(), t
+        if auto_reset and od.any():
+            idx = np.nonzero(od)[0]
+            lvl[idx] = (lvl[idx] + stride) % pool.n_levels
+            oenv.reset(idx, lvl[idx])
+        if t % check_every == 0 or t == steps - 1:
+            assert (env.game.board.cpu().numpy() == oenv.boards).all(), t
+            assert (env.game.goals.cpu().numpy() == oenv.goals).all(), t
+            st, ost = env.game.state_numpy(), oenv.states
+            for f in st.dtype.names:
+                assert (st[f] == ost[f]).all(), (f, t)
+    return env
+
+
+def test_batch_vs_oracle_prune_spawn(sl):
+    _oracle_vs_device(sl, "prune-spawn", 384, 150, seed=0, aseed=3, auto_reset=False)
+
+
+def test_batch_vs_oracle_auto_reset(sl):
+    _oracle_vs_device(sl, "append-spawn", 250, 200, seed=9, aseed=4, auto_reset=True)
+
+
+def test_rollout_equals_steps_and_placement_independence(sl):
+    lv = gu.levels("prune-spawn")
+    pool = sl.game.LevelPool(lv)
+    n, T = 256, 40
+    acts = torch.from_numpy(np.random.RandomState(1).randint(9, size=(T, n)).astype(np.uint8)).cuda()
+    a = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False)
+    a.seed(3); a.reset()
+    b = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False)
+    b.seed(3); b.reset()
+    r_roll, d_roll = a.rollout(acts)
+    for t in range(T):
+        _, r, d, _ = b.step(acts[t])
+        assert (r == r_roll[t]).all() and (d == (d_roll[t] != 0)).all()
+    assert (a.game.board == b.game.board).all() and (a.game.goals == b.game.goals).all()
+    assert (a.game.state == b.game.state).all()
+    # the second half of the envs, run as their own shard (env_id0 = n/2), gives identical results
+    h = n // 2
+    c = sl.env.SafeLifeEnv(pool, num_envs=h, env_id0=h, global_counter=None, compute_obs=False)
+    c.seed(3); c.reset()
+    r_c, _ = c.rollout(acts[:, h:].contiguous())
+    assert (r_c == r_roll[:, h:]).all()
+    assert (c.game.board == a.game.board[h:]).all() and (c.game.goals == a.game.goals[h:]).all()
+
+
+def test_large_board_vs_oracle(sl):
+    rng = np.random.RandomState(5)
+    vals = np.array([0, 1033, 16, 1041, 521, 32788, 1688], np.uint16)
+    p = np.array([60, 25, 5, 4, 3, 2, 1], float) / 100
+    boards = vals[rng.choice(len(vals), size=(3, 256, 256), p=p)]
+    out, ctr = dev_advance(sl, boards, 0.3, seed=11, env0=5)
+    for i in range(3):
+        o, c = slo.advance_board(boards[i], 0.3, seed=11, env=5 + i)
+        assert (out[i] == o).all() and ctr[i] == c
+    # idempotence-style property at full size: a board of still lifes and walls is a fixed point
+    still = np.zeros((4096, 26, 26), np.uint16)
+    still[:, 3:5, 3:5] = 1033
+    still[:, 10, :] = 16
+    out, _ = dev_advance(sl, still, 0.3, seed=0, env0=0)
+    assert (out == still).all()
+
+
+def test_error_behaviour(sl):
+    L = sl.lib.load()
+    b = torch.zeros((1, 2, 8), dtype=torch.uint16, device="cuda")
+    p = torch.zeros(1, device="cuda")
+    rc = L.slb_advance_board(b.data_ptr(), b.data_ptr() + 64, 1, 2, 8, p.data_ptr(), 0, 0, None, 1,
+                             None, None)
+    assert rc == sl.lib.SLB_ERR_INVALID and b"3x3" in L.slb_last_error()
+    rc = L.slb_advance_board(b.data_ptr(), b.data_ptr(), 1, 4, 4, p.data_ptr(), 0, 0, None, 1, None, None)
+    assert rc == sl.lib.SLB_ERR_INVALID
+
+
+def test_stats_accumulate(sl):
+    lv = gu.levels("append-still")
+    pool = sl.game.LevelPool(lv)
+    env = sl.env.SafeLifeEnv(pool, num_envs=300, global_counter=None, compute_obs=False, time_limit=3)
+    env.seed(0); env.reset()
+    stats = torch.zeros(8, dtype=torch.int64, device="cuda")
+    tot_r, tot_d = 0, 0
+    for t in range(5):
+        _, r, d, _ = env.step(np.random.RandomState(t).randint(9, size=300))
+        sl.lib.check(sl.lib.load().slb_accumulate_stats(300, env.game.state.data_ptr(), r.data_ptr(),
+                                                        env._done.data_ptr(), stats.data_ptr(),
+                                                        sl.lib.current_stream()))
+        tot_r += int(r.sum()); tot_d += int(d.sum())
+    s = stats.cpu().numpy()
+    assert s[0] == tot_r and s[1] == tot_d and s[6] == 1500
