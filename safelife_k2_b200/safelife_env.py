@@ -34,6 +34,7 @@ class SafeLifeEnv(object):
     env_id0 = 0          # global index of this shard's first env (placement-independent streams)
     auto_reset = False   # reset finished envs inside the step kernel (ContinuingEnv-like)
     compute_obs = True   # False: step()/reset() return obs=None (policy reads game.board itself)
+    level_ids = None     # first level of each env (default: (global env index) % pool size)
 
     def __init__(self, level_iterator, **kwargs):
         """level_iterator: a LevelPool, or anything LevelPool accepts (structured level array,
@@ -50,7 +51,10 @@ class SafeLifeEnv(object):
         dev = self.pool.device
         self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
         self._done = torch.zeros(self.num_envs, dtype=torch.uint8, device=dev)
-        self._next_level = (np.arange(self.num_envs) + self.env_id0) % self.pool.n_levels
+        if self.level_ids is None:
+            self._next_level = (np.arange(self.num_envs) + self.env_id0) % self.pool.n_levels
+        else:
+            self._next_level = np.asarray(self.level_ids, dtype=np.int64).reshape(self.num_envs) % self.pool.n_levels
         self.seed()
 
     # ------------------------------------------------------------------------------------------

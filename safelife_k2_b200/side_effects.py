@@ -102,7 +102,7 @@ def side_effect_score(game, num_samples=1000, include=None, exclude=None, emd=Tr
     """
     pool = game.pool
     lv = game.level_id.long()
-    board0 = pool.board[lv]
+    board0 = pool.board.view(torch.int16)[lv].view(torch.uint16)  # uint16 has no index kernel
     ctr = game.rng_counter.contiguous()
     keys, counts, nkeys = side_effect_counts(board0, game.board, game.num_steps.contiguous(),
                                              game.spawn_prob, num_samples, game.seed, game.env_id0,

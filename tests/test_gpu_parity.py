@@ -91,7 +91,7 @@ def test_env_trace(sl, archive):
     l0 = int(tr["level0"])
     pool = sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 2))
     env = sl.env.SafeLifeEnv(pool, num_envs=1, env_id0=int(tr["env_id"]), global_counter=None,
-                             compute_obs=False)
+                             compute_obs=False, level_ids=[0])
     env.seed(int(tr["seed"]))
     env.reset()
     for t, a in enumerate(tr["actions"]):
