@@ -316,9 +316,10 @@ int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, i
         return fail(SLB_ERR_INVALID, "num_samples must fit the uint16 count maps (<= 65535)");
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (fast_shape(h, w)) {
+    if (fast_shape(h, w) &&
         launch_side_effect_fast(d_board0, d_board1, n, h, w, d_num_steps, num_samples, d_spawn_prob,
-                                seed, env_id0, d_counters, kmax, d_keys, d_counts, d_nkeys, st);
+                                seed, env_id0, d_counters, kmax, d_keys, d_counts, d_nkeys,
+                                smem_optin() - kSmemStatic, st)) {
         SLB_LAUNCHED();
         return SLB_OK;
     }

@@ -1,0 +1,253 @@
+// slb_planes.cuh — bit-sliced SafeLife on one warp per board (H <= 32 rows across lanes, W <= 32
+// cells across the bits of one 32-bit word, 16 bit-planes per lane in registers).
+//
+// A board row r lives in lane r as P[b] (b = cell bit 0..15): bit c of P[b] = bit b of cell (r, c).
+// Bits >= W of every plane are kept zero; lanes >= H hold zeros.  Vertical neighbours come from
+// warp shuffles (toroidal: lane (r +- 1) mod H), horizontal ones from rotations within W bits.
+// Semantics follow the reference exactly; parity is tested bit for bit.
+#pragma once
+#include "slb_common.cuh"
+
+namespace slb {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+struct Geo {
+    int h, w;
+    int up, dn;      // source lanes of the rows above / below this lane (toroidal)
+    uint32_t wmask;  // low W bits
+    bool row;        // lane < h
+};
+
+__device__ __forceinline__ Geo make_geo(int h, int w) {
+    Geo g;
+    int lane = threadIdx.x & 31;
+    g.h = h; g.w = w;
+    g.row = lane < h;
+    g.up = g.row ? (lane == 0 ? h - 1 : lane - 1) : lane;
+    g.dn = g.row ? (lane == h - 1 ? 0 : lane + 1) : lane;
+    g.wmask = (w >= 32) ? 0xffffffffu : ((1u << w) - 1u);
+    return g;
+}
+
+// value of the LEFT neighbour (cell c-1) at bit c / of the RIGHT neighbour (cell c+1) at bit c
+__device__ __forceinline__ uint32_t from_left(uint32_t x, const Geo &g) {
+    return ((x << 1) | (x >> (g.w - 1))) & g.wmask;
+}
+__device__ __forceinline__ uint32_t from_right(uint32_t x, const Geo &g) {
+    return ((x >> 1) | (x << (g.w - 1))) & g.wmask;
+}
+
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) { return a ^ b ^ c; }
+__device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) {
+    return (a & b) | (c & (a | b));
+}
+__device__ __forceinline__ uint32_t or3(uint32_t a, uint32_t b, uint32_t c) { return a | b | c; }
+
+// ---------------------------------------------------------------------------------------------
+// 32 cells x 16 bits  <->  16 planes x 32 bits, in registers.
+// x[j] (j < 16) = cell(2j) | cell(2j+1) << 16 (the row as it lies in memory, zero padded).
+// Step 1 (PRMT): y[j] = cell(j) | cell(j+16) << 16.  Step 2: a 16x16 bit transpose carried out on
+// both 16-bit halves at once (block-swap stages 8, 4, 2, 1; stage 8 is a byte permute).
+// The transpose is an involution, so the inverse runs the same stages and then undoes step 1.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void transpose16_halves(uint32_t y[16]) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {  // stage 8: rows i <-> i+8, swap bytes
+        uint32_t a = y[i], b = y[i + 8];
+        y[i] = __byte_perm(a, b, 0x6240);      // a0 b0 a2 b2
+        y[i + 8] = __byte_perm(a, b, 0x7351);  // a1 b1 a3 b3
+    }
+#pragma unroll
+    for (int s = 4; s >= 1; s >>= 1) {
+        const uint32_t m = (s == 4) ? 0x0f0f0f0fu : (s == 2) ? 0x33333333u : 0x55555555u;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            if (i & s) continue;
+            uint32_t a = y[i], b = y[i + s];
+            y[i] = (a & m) | ((b << s) & ~m);
+            y[i + s] = ((a >> s) & m) | (b & ~m);
+        }
+    }
+}
+
+__device__ __forceinline__ void cells_to_planes(const uint32_t x[16], uint32_t P[16]) {
+#pragma unroll
+    for (int j = 0; j < 16; j++)
+        P[j] = __byte_perm(x[j >> 1], x[8 + (j >> 1)], (j & 1) ? 0x7632 : 0x5410);
+    transpose16_halves(P);
+}
+
+__device__ __forceinline__ void planes_to_cells(const uint32_t P[16], uint32_t x[16]) {
+    uint32_t y[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) y[j] = P[j];
+    transpose16_halves(y);
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        // y[2j] = cell(2j) | cell(2j+16)<<16, y[2j+1] = cell(2j+1) | cell(2j+17)<<16
+        x[j] = __byte_perm(y[2 * j], y[2 * j + 1], 0x5410);      // cell(2j) | cell(2j+1)<<16
+        x[8 + j] = __byte_perm(y[2 * j], y[2 * j + 1], 0x7632);  // cell(2j+16) | cell(2j+17)<<16
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Staging between the uint16 [H,W] layout in global memory and per-lane planes.  `sm` is this
+// warp's shared staging area of H * S uint16 (S = padded row stride, see row_stride()).
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ int row_stride(int w) {
+    int s = (w + 1) & ~1;           // even
+    if (((s >> 1) & 1) == 0) s += 2;  // S/2 odd -> conflict-free 32-bit row reads across lanes
+    return s;
+}
+
+// vec: all boards are 8-byte aligned and S == w (then the smem image equals the memory image)
+__device__ __forceinline__ void load_planes(const uint16_t *__restrict__ src, uint16_t *sm, int h,
+                                            int w, bool vec, uint32_t P[16]) {
+    const int lane = threadIdx.x & 31, cells = h * w, S = row_stride(w);
+    __syncwarp();
+    if (vec) {
+        const uint2 *s2 = reinterpret_cast<const uint2 *>(src);
+        uint2 *d2 = reinterpret_cast<uint2 *>(sm);
+        for (int j = lane; j < (cells >> 2); j += 32) d2[j] = s2[j];
+    } else {
+        for (int e = lane; e < cells; e += 32) {
+            int r = e / w, c = e - r * w;
+            sm[r * S + c] = src[e];
+        }
+    }
+    __syncwarp();
+    uint32_t x[16];
+    const uint32_t *row = reinterpret_cast<const uint32_t *>(sm) + lane * (S >> 1);
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        uint32_t v = 0;
+        if (lane < h && 2 * j < w) {
+            v = row[j];
+            if (2 * j + 1 >= w) v &= 0xffffu;
+        }
+        x[j] = v;
+    }
+    cells_to_planes(x, P);
+}
+
+__device__ __forceinline__ void store_planes(uint16_t *__restrict__ dst, uint16_t *sm, int h, int w,
+                                             bool vec, const uint32_t P[16]) {
+    const int lane = threadIdx.x & 31, cells = h * w, S = row_stride(w);
+    uint32_t x[16];
+    planes_to_cells(P, x);
+    __syncwarp();
+    uint32_t *row = reinterpret_cast<uint32_t *>(sm) + lane * (S >> 1);
+#pragma unroll
+    for (int j = 0; j < 16; j++)
+        if (lane < h && 2 * j < w) row[j] = x[j];  // a padding half-word may be written: never read back
+    __syncwarp();
+    if (vec) {
+        const uint2 *s2 = reinterpret_cast<const uint2 *>(sm);
+        uint2 *d2 = reinterpret_cast<uint2 *>(dst);
+        for (int j = lane; j < (cells >> 2); j += 32) d2[j] = s2[j];
+    } else {
+        for (int e = lane; e < cells; e += 32) {
+            int r = e / w, c = e - r * w;
+            dst[e] = sm[r * S + c];
+        }
+    }
+    __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
+// One advance_board step on the planes (advance_board.c:34-120, closed form of Appendix A).
+// Returns the env's updated draw counter.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g, uint64_t thr,
+                                                   uint64_t seed, uint64_t env, uint64_t counter) {
+    const uint32_t a = P[0];
+    const uint32_t d2 = P[3] | P[8];  // exit bit aliases destructible (advance_board.c:44-46)
+    // ---- vertical 3-row combination (rows r-1, r, r+1) ----
+#define SLB_UP(v) __shfl_sync(FULL, (v), g.up)
+#define SLB_DN(v) __shfl_sync(FULL, (v), g.dn)
+    uint32_t v0, v1;  // alive count of the column triple, 2 bits
+    {
+        uint32_t u = SLB_UP(a), d = SLB_DN(a);
+        v0 = xor3(a, u, d);
+        v1 = maj3(a, u, d);
+    }
+    uint32_t vfl[6];  // OR over the column triple: preserving, inhibiting, spawning, spawner colours r/g/b
+    {
+        const uint32_t src[6] = {P[5], P[6], P[7], P[7] & P[9], P[7] & P[10], P[7] & P[11]};
+#pragma unroll
+        for (int k = 0; k < 6; k++) vfl[k] = or3(src[k], SLB_UP(src[k]), SLB_DN(src[k]));
+    }
+    uint32_t f0[4], f1[4];  // count (2 bits) of alive cells carrying D2 / R / G / B in the column triple
+    {
+        const uint32_t src[4] = {a & d2, a & P[9], a & P[10], a & P[11]};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t u = SLB_UP(src[k]), d = SLB_DN(src[k]);
+            f0[k] = xor3(src[k], u, d);
+            f1[k] = maj3(src[k], u, d);
+        }
+    }
+#undef SLB_UP
+#undef SLB_DN
+    // ---- horizontal combination of the three column triples ----
+    uint32_t is3, is4;
+    {
+        uint32_t l0 = from_left(v0, g), r0 = from_right(v0, g);
+        uint32_t l1 = from_left(v1, g), r1 = from_right(v1, g);
+        uint32_t s0 = xor3(l0, v0, r0), c0 = maj3(l0, v0, r0);
+        uint32_t s1 = xor3(l1, v1, r1), c1 = maj3(l1, v1, r1);
+        uint32_t n1 = c0 ^ s1, k = c0 & s1, n2 = c1 ^ k;  // n = s0 + 2 n1 + 4 n2 + 8 (c1 & k), n <= 9
+        is3 = s0 & n1 & ~n2;
+        is4 = ~s0 & ~n1 & n2;  // n2 set implies the 8s bit (c1 & k) is clear
+    }
+    uint32_t fl[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) fl[k] = or3(from_left(vfl[k], g), vfl[k], from_right(vfl[k], g));
+    uint32_t two[4];  // ">= 2 alive cells in the 3x3 carry the flag"
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint32_t hi = or3(from_left(f1[k], g), f1[k], from_right(f1[k], g));
+        two[k] = hi | maj3(from_left(f0[k], g), f0[k], from_right(f0[k], g));
+    }
+    const uint32_t PR = fl[0], IH = fl[1], SP = fl[2];
+    const uint32_t tR = two[1] | fl[3], tG = two[2] | fl[4], tB = two[3] | fl[5];
+    // ---- rule ----
+    const uint32_t fz = P[4];
+    const uint32_t die = a & ~(fz | PR | is3 | is4);
+    const uint32_t open = ~a & ~(fz | IH) & g.wmask;  // dead, not frozen, not inhibited
+    const uint32_t birth = open & is3;
+    const uint32_t elig = open & ~is3 & SP;  // the cells that consume a draw (advance_board.c:110)
+    uint32_t spawn = 0;
+    if (__any_sync(FULL, elig != 0)) {
+        // raster-order rank of every eligible cell: exclusive prefix over rows, then within the row
+        int cnt = __popc(elig), incl = cnt;
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(FULL, incl, o);
+            if (lane >= o) incl += t;
+        }
+        uint64_t base = counter + (uint64_t)(incl - cnt);
+        uint32_t e = elig;
+        while (e) {
+            uint32_t bit = e & (0u - e);
+            e ^= bit;
+            if (stream_u53(seed, env, base) < thr) spawn |= bit;
+            base++;
+        }
+        counter += (uint64_t)__shfl_sync(FULL, incl, 31);
+    }
+    const uint32_t born = birth | spawn;
+    const uint32_t keep = ~(die | born);
+#pragma unroll
+    for (int b = 0; b < 16; b++) P[b] &= keep;  // killed cells lose everything; births discard residue
+    P[0] |= born;
+    P[3] |= (birth & two[0]) | spawn;  // spawned cells are always destructible
+    P[9] |= born & tR;
+    P[10] |= born & tG;
+    P[11] |= born & tB;
+    return counter;
+}
+
+}  // namespace slb
