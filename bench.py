@@ -163,7 +163,7 @@ def run_b200(args):
     def step(i):
         e = envs[i % ring]
         g = e.game
-        _lib.check(lib.slb_env_step(pool.c, n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+        _lib.check(lib.slb_env_step(pool.c, n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
                                     acts[i % n_act].data_ptr(), 1000, 0, g.env_id0, e._reward.data_ptr(),
                                     e._done.data_ptr(), e._stride(), stream.cuda_stream))
 

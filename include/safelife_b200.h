@@ -25,13 +25,14 @@
  */
 #ifndef SAFELIFE_B200_H
 #define SAFELIFE_B200_H
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define SLB_ABI_VERSION 1
+#define SLB_ABI_VERSION 2
 
 typedef enum {
     SLB_OK = 0,
@@ -76,10 +77,34 @@ typedef struct {
     const double *min_performance;  /* [P] */
     int32_t *baseline;              /* [P]   written by slb_pool_prepare */
     uint32_t *exit_mask;            /* [P,H,words_per_row] written by slb_pool_prepare */
+    void *board_res;                /* [P] boards in the RESIDENT format, written by slb_pool_prepare */
+    void *goals_res;                /* [P] goals  in the RESIDENT format, written by slb_pool_prepare */
+    uint32_t *plane_bits;           /* [2] OR of every board / goals cell seen (pool + imports); zeroed
+                                       by the caller, maintained by slb_pool_prepare / slb_resident_import */
 } slb_pool;
 
-/* Fills pool->baseline (performance_ratio's baseline_score, safelife_game.py:622) and
- * pool->exit_mask (update_exit_locs, :528-529). */
+/* ---- RESIDENT env state ------------------------------------------------------------------------
+ * Between steps an env's board and goals live on the device in the layout the kernels compute in,
+ * not in the reference's uint16 [H,W] layout:
+ *   - 4 <= H, W <= 32 (the 26x26 benchmark levels): bit-sliced, 64*H bytes per board — 4 plane
+ *     groups x H rows x 16 bytes; group g of row r holds that row's 32-bit column masks of planes
+ *     {alive 0, frozen 4, red 9, green 10}, {blue 11, destructible 3, pushable 2, pullable 15},
+ *     {agent 1, preserving 5, inhibiting 6, exit 8}, {spawning 7, bits 12, 13, 14} for g = 0..3.
+ *     Groups 2/3 are only touched when some cell of the pool has one of their bits (plane_bits).
+ *   - any other shape >= 3x3: the uint16 [H,W] cells themselves (2*H*W bytes per board).
+ * Resident buffers are caller-allocated, N * slb_resident_bytes(h, w) bytes, 16-byte aligned and
+ * ZERO-INITIALISED; slb_resident_import / _export convert from / to uint16 [N,H,W] cells (the
+ * format of every other boundary: level pool, speedups.advance_board, side effects, observations).
+ */
+size_t slb_resident_bytes(int h, int w);
+/* d_cells [N,H,W] uint16 -> d_res.  pool_plane_bits: &pool->plane_bits[0] for boards, [1] for
+ * goals (device pointer; may be NULL for a conversion that no env kernel will read). */
+int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int w,
+                        uint32_t *pool_plane_bits, void *stream);
+int slb_resident_export(const void *d_res, uint16_t *d_cells, int n, int h, int w, void *stream);
+
+/* Fills pool->baseline (performance_ratio's baseline_score, safelife_game.py:622),
+ * pool->exit_mask (update_exit_locs, :528-529), the resident copies of the levels and plane_bits. */
 int slb_pool_prepare(const slb_pool *pool, void *stream);
 
 /* ---- A1-A4: speedups.advance_board for N boards (module.c:19-44 -> advance_board.c:34-120) ----
@@ -97,29 +122,36 @@ int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, 
                            const float *h_spawn_prob, uint64_t seed, uint64_t env_id0,
                            uint64_t *h_counters, int k_steps);
 
-/* ---- A17: reset (safelife_env.py:188-198; revert/deserialize safelife_game.py:196-212,229-234) --
+/* In every function below d_board / d_goals are RESIDENT buffers of N envs (see above).
+ *
+ * ---- A17: reset (safelife_env.py:188-198; revert/deserialize safelife_game.py:196-212,229-234) --
  * For every env i with d_mask == NULL or d_mask[i] != 0: load level d_level_ids[i]. */
 int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const uint8_t *d_mask,
-                  uint16_t *d_board, uint16_t *d_goals, slb_env_state *d_state, void *stream);
+                  void *d_board, void *d_goals, slb_env_state *d_state, void *stream);
 
 /* ---- A7/A8: execute_action (safelife_game.py:347-393, move_agent :308-345) -----------------------
  * d_actions: [N] uint8, 0 NULL, 1-4 MOVE U/R/D/L, 5-8 TOGGLE U/R/D/L (safelife_env.py:61-71).
  * Uses and updates d_state (agent_x/y, orientation, game_over); can_exit is read from
  * d_state[i].can_exit.  d_reward: [N] int32 action reward (0 / +1). */
-int slb_execute_action(uint16_t *d_board, int n, int h, int w, slb_env_state *d_state,
+int slb_execute_action(const slb_pool *pool, int n, void *d_board, slb_env_state *d_state,
                        const uint8_t *d_actions, int32_t *d_reward, void *stream);
+
+/* ---- A4: SafeLifeGame.advance_board (safelife_game.py:657-660) on resident state: num_steps += 1,
+ * board then goals (the order the env's stream is consumed in), spawn_prob of each env's level. */
+int slb_game_advance(const slb_pool *pool, int n, void *d_board, void *d_goals,
+                     slb_env_state *d_state, uint64_t seed, uint64_t env_id0, void *stream);
 
 /* ---- A9-A11: current_points, performance_ratio, can_exit (safelife_game.py:590-631, 522-526) ----
  * Any output pointer may be NULL.  Does not modify state. */
-int slb_points_and_performance(const slb_pool *pool, int n, const uint16_t *d_board,
-                               const uint16_t *d_goals, const slb_env_state *d_state,
+int slb_points_and_performance(const slb_pool *pool, int n, const void *d_board,
+                               const void *d_goals, const slb_env_state *d_state,
                                int32_t *d_points, int32_t *d_completed, int32_t *d_possible,
                                uint8_t *d_can_exit, void *stream);
 
 /* update_exit_colors (safelife_game.py:531-537): evaluates can_exit() on the current board/goals,
  * repaints the level's initial exit cells (272 / 784) and refreshes d_state[i].can_exit,
  * .completed, .possible. */
-int slb_update_exit_colors(const slb_pool *pool, int n, uint16_t *d_board, const uint16_t *d_goals,
+int slb_update_exit_colors(const slb_pool *pool, int n, void *d_board, const void *d_goals,
                            slb_env_state *d_state, void *stream);
 
 /* ---- A12: one SafeLifeEnv.step for N envs, fused (safelife_env.py:157-186) ----------------------
@@ -127,7 +159,7 @@ int slb_update_exit_colors(const slb_pool *pool, int n, uint16_t *d_board, const
  * update_exit_colors -> done.  d_reward [N] int32, d_done [N] uint8 (either may be NULL).
  * auto_reset_stride > 0: an env that finishes this step is reset (after its outputs are written)
  * to level (level_id + auto_reset_stride) % n_levels. */
-int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
                  slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
                  uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
                  void *stream);
@@ -135,14 +167,14 @@ int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goa
 /* T fused env-steps with pre-staged actions: d_actions [T,N] uint8, d_reward [T,N] int32,
  * d_done [T,N] uint8 (outputs may be NULL).  Board state stays on chip between steps when the
  * shape has a fast path; otherwise this loops slb_env_step. */
-int slb_env_rollout(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
                     slb_env_state *d_state, const uint8_t *d_actions, int t_steps, int time_limit,
                     uint64_t seed, uint64_t env_id0, int32_t *d_reward, uint8_t *d_done,
                     int auto_reset_stride, void *stream);
 
 /* Host-buffer step (the call a CPU-side policy makes): actions in, reward/done out, state stays
  * resident on the device.  Synchronous. */
-int slb_env_step_host(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
                       uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                       int auto_reset_stride, void *stream);
@@ -167,9 +199,14 @@ int slb_accumulate_stats(int n, const slb_env_state *d_state, const int32_t *d_r
 
 /* ---- "next" row 1: observation (safelife_env.py:125-155, helper_utils.py:41-74) ------------------
  * d_obs: [N,vh,vw] uint16 words (bit b = channel b).  Channel split is a view-level bit test. */
-int slb_get_obs(const slb_pool *pool, int n, const uint16_t *d_board, const uint16_t *d_goals,
+int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
                 const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
                 uint16_t *d_obs, void *stream);
+
+/* The channel split of safelife_env.py:152-154 for M packed words: d_out [M, n_channels] uint16,
+ * d_out[m, c] = (d_words[m] >> d_channels[c]) & 1.  n_channels <= 16; d_out 4-byte aligned. */
+int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *d_channels, int n_channels,
+                     uint16_t *d_out, void *stream);
 
 #ifdef __cplusplus
 }

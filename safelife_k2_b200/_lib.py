@@ -31,21 +31,26 @@ class Pool(C.Structure):
         ("agent_x", C.c_void_p), ("agent_y", C.c_void_p), ("orientation", C.c_void_p),
         ("spawn_prob", C.c_void_p), ("min_performance", C.c_void_p),
         ("baseline", C.c_void_p), ("exit_mask", C.c_void_p),
+        ("board_res", C.c_void_p), ("goals_res", C.c_void_p), ("plane_bits", C.c_void_p),
     ]
 
 
 # every symbol include/safelife_b200.h declares: name -> (restype, argtypes)
-_vp, _i, _u64 = C.c_void_p, C.c_int, C.c_uint64
+_vp, _i, _u64, _sz = C.c_void_p, C.c_int, C.c_uint64, C.c_size_t
 _PP = C.POINTER(Pool)
 SYMBOLS = {
     "slb_last_error": (C.c_char_p, []),
     "slb_abi_version": (_i, []),
     "slb_launch_count": (_u64, []),
     "slb_pool_prepare": (_i, [_PP, _vp]),
+    "slb_resident_bytes": (_sz, [_i, _i]),
+    "slb_resident_import": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "slb_resident_export": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "slb_advance_board": (_i, [_vp, _vp, _i, _i, _i, _vp, _u64, _u64, _vp, _i, _vp, _vp]),
     "slb_advance_board_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _u64, _u64, _vp, _i]),
     "slb_env_reset": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
-    "slb_execute_action": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "slb_execute_action": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp]),
+    "slb_game_advance": (_i, [_PP, _i, _vp, _vp, _vp, _u64, _u64, _vp]),
     "slb_points_and_performance": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "slb_update_exit_colors": (_i, [_PP, _i, _vp, _vp, _vp, _vp]),
     "slb_env_step": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _vp]),
@@ -55,6 +60,7 @@ SYMBOLS = {
                                     _vp, _vp, _vp, _vp]),
     "slb_accumulate_stats": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
     "slb_get_obs": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "slb_obs_channels": (_i, [_vp, _sz, _vp, _i, _vp, _vp]),
 }
 
 _lib = None
@@ -74,7 +80,7 @@ def load():
             fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
             fn.restype = res
             fn.argtypes = args
-        if lib.slb_abi_version() != 1:
+        if lib.slb_abi_version() != 2:
             raise ImportError("libsafelife_b200.so ABI version mismatch")
         _lib = lib
     return _lib

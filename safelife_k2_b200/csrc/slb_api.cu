@@ -53,8 +53,10 @@ int check_pool(const slb_pool *p) {
     if (p->n_levels <= 0) return fail(SLB_ERR_INVALID, "pool has no levels");
     if (p->words_per_row != (p->w + 31) / 32) return fail(SLB_ERR_INVALID, "pool.words_per_row");
     if (!p->board || !p->goals || !p->agent_x || !p->agent_y || !p->orientation ||
-        !p->spawn_prob || !p->min_performance || !p->baseline || !p->exit_mask)
+        !p->spawn_prob || !p->min_performance || !p->baseline || !p->exit_mask || !p->plane_bits)
         return fail(SLB_ERR_INVALID, "pool has NULL arrays");
+    if (fast_shape(p->h, p->w) && (!p->board_res || !p->goals_res))
+        return fail(SLB_ERR_INVALID, "pool.board_res / goals_res are required for %dx%d boards", p->h, p->w);
     return check_shape(0, p->h, p->w);
 }
 
@@ -86,10 +88,54 @@ const char *slb_last_error(void) { return g_err; }
 int slb_abi_version(void) { return SLB_ABI_VERSION; }
 uint64_t slb_launch_count(void) { return g_launches.load(); }
 
+size_t slb_resident_bytes(int h, int w) {
+    if (h < 3 || w < 3) return 0;
+    return fast_shape(h, w) ? resident_words(h) * 4 : (size_t)h * w * 2;
+}
+
+int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int w,
+                        uint32_t *pool_plane_bits, void *stream) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!d_cells || !d_res) return fail(SLB_ERR_INVALID, "slb_resident_import: NULL pointer");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!fast_shape(h, w)) {
+        SLB_CUDA(cudaMemcpyAsync(d_res, d_cells, (size_t)n * h * w * 2, cudaMemcpyDeviceToDevice, st));
+        return SLB_OK;
+    }
+    if ((uintptr_t)d_res % 16) return fail(SLB_ERR_INVALID, "resident buffers must be 16-byte aligned");
+    res_import_kernel<<<(n + RES_WARPS - 1) / RES_WARPS, RES_WARPS * 32, 0, st>>>(
+        d_cells, (uint32_t *)d_res, n, h, w, pool_plane_bits, fast_vec_ok(h, w, d_cells, d_cells));
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_resident_export(const void *d_res, uint16_t *d_cells, int n, int h, int w, void *stream) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!d_cells || !d_res) return fail(SLB_ERR_INVALID, "slb_resident_export: NULL pointer");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!fast_shape(h, w)) {
+        SLB_CUDA(cudaMemcpyAsync(d_cells, d_res, (size_t)n * h * w * 2, cudaMemcpyDeviceToDevice, st));
+        return SLB_OK;
+    }
+    if ((uintptr_t)d_res % 16) return fail(SLB_ERR_INVALID, "resident buffers must be 16-byte aligned");
+    res_export_kernel<<<(n + RES_WARPS - 1) / RES_WARPS, RES_WARPS * 32, 0, st>>>(
+        (const uint32_t *)d_res, d_cells, n, h, w, fast_vec_ok(h, w, d_cells, d_cells));
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
 int slb_pool_prepare(const slb_pool *pool, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     pool_prepare_kernel<<<pool->n_levels, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool);
     SLB_LAUNCHED();
+    if (fast_shape(pool->h, pool->w)) {
+        if (int rc = slb_resident_import(pool->board, pool->board_res, pool->n_levels, pool->h, pool->w,
+                                         pool->plane_bits, stream)) return rc;
+        if (int rc = slb_resident_import(pool->goals, pool->goals_res, pool->n_levels, pool->h, pool->w,
+                                         pool->plane_bits + 1, stream)) return rc;
+    }
     return SLB_OK;
 }
 
@@ -173,54 +219,99 @@ int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, 
     return rc;
 }
 
+#define RES_GRID(n) (((n) + RES_WARPS - 1) / RES_WARPS), RES_WARPS * 32, 0
+
 int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const uint8_t *d_mask,
-                  uint16_t *d_board, uint16_t *d_goals, slb_env_state *d_state, void *stream) {
+                  void *d_board, void *d_goals, slb_env_state *d_state, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_level_ids || !d_board || !d_goals || !d_state)
         return fail(SLB_ERR_INVALID, "slb_env_reset: bad arguments");
     if (n == 0) return SLB_OK;
-    reset_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool, d_level_ids, d_mask,
-                                                                      d_board, d_goals, d_state);
+    if (fast_shape(pool->h, pool->w))
+        res_reset_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(*pool, n, d_level_ids, d_mask,
+                                                              (uint32_t *)d_board, (uint32_t *)d_goals, d_state);
+    else
+        reset_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
+            *pool, d_level_ids, d_mask, (uint16_t *)d_board, (uint16_t *)d_goals, d_state);
     SLB_LAUNCHED();
     return SLB_OK;
 }
 
-int slb_execute_action(uint16_t *d_board, int n, int h, int w, slb_env_state *d_state,
+int slb_execute_action(const slb_pool *pool, int n, void *d_board, slb_env_state *d_state,
                        const uint8_t *d_actions, int32_t *d_reward, void *stream) {
-    if (int rc = check_shape(n, h, w)) return rc;
-    if (!d_board || !d_state || !d_actions) return fail(SLB_ERR_INVALID, "slb_execute_action: NULL pointer");
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_board || !d_state || !d_actions)
+        return fail(SLB_ERR_INVALID, "slb_execute_action: bad arguments");
     if (n == 0) return SLB_OK;
-    execute_action_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(d_board, n, h, w, d_state,
-                                                                           d_actions, d_reward);
+    if (fast_shape(pool->h, pool->w))
+        res_action_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(*pool, n, (uint32_t *)d_board, d_state,
+                                                               d_actions, d_reward);
+    else
+        execute_action_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+            (uint16_t *)d_board, n, pool->h, pool->w, d_state, d_actions, d_reward);
     SLB_LAUNCHED();
     return SLB_OK;
 }
 
-int slb_points_and_performance(const slb_pool *pool, int n, const uint16_t *d_board,
-                               const uint16_t *d_goals, const slb_env_state *d_state,
+int slb_game_advance(const slb_pool *pool, int n, void *d_board, void *d_goals,
+                     slb_env_state *d_state, uint64_t seed, uint64_t env_id0, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_board || !d_goals || !d_state)
+        return fail(SLB_ERR_INVALID, "slb_game_advance: bad arguments");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fast_shape(pool->h, pool->w)) {
+        res_advance_kernel<<<RES_GRID(n), st>>>(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals,
+                                               d_state, seed, env_id0);
+    } else {
+        size_t bytes = (size_t)pool->h * pool->w * 2;
+        if (bytes + kSmemStatic > smem_optin())
+            return fail(SLB_ERR_UNSUPPORTED, "game advance needs the %dx%d board in shared memory",
+                        pool->h, pool->w);
+        if (int rc = allow_smem(game_advance_generic_kernel, bytes)) return rc;
+        game_advance_generic_kernel<<<n, GEN_THREADS, bytes, st>>>(
+            *pool, (uint16_t *)d_board, (uint16_t *)d_goals, d_state, seed, env_id0);
+    }
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_points_and_performance(const slb_pool *pool, int n, const void *d_board,
+                               const void *d_goals, const slb_env_state *d_state,
                                int32_t *d_points, int32_t *d_completed, int32_t *d_possible,
                                uint8_t *d_can_exit, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_board || !d_goals || !d_state) return fail(SLB_ERR_INVALID, "slb_points: bad arguments");
     if (n == 0) return SLB_OK;
-    points_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
-        *pool, d_board, d_goals, d_state, d_points, d_completed, d_possible, d_can_exit);
+    if (fast_shape(pool->h, pool->w))
+        res_score_kernel<false><<<RES_GRID(n), (cudaStream_t)stream>>>(
+            *pool, n, (uint32_t *)d_board, (const uint32_t *)d_goals, (slb_env_state *)d_state, d_points,
+            d_completed, d_possible, d_can_exit);
+    else
+        points_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
+            *pool, (const uint16_t *)d_board, (const uint16_t *)d_goals, d_state, d_points, d_completed,
+            d_possible, d_can_exit);
     SLB_LAUNCHED();
     return SLB_OK;
 }
 
-int slb_update_exit_colors(const slb_pool *pool, int n, uint16_t *d_board, const uint16_t *d_goals,
+int slb_update_exit_colors(const slb_pool *pool, int n, void *d_board, const void *d_goals,
                            slb_env_state *d_state, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_board || !d_goals || !d_state)
         return fail(SLB_ERR_INVALID, "slb_update_exit_colors: bad arguments");
     if (n == 0) return SLB_OK;
-    exit_colors_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool, d_board, d_goals, d_state);
+    if (fast_shape(pool->h, pool->w))
+        res_score_kernel<true><<<RES_GRID(n), (cudaStream_t)stream>>>(
+            *pool, n, (uint32_t *)d_board, (const uint32_t *)d_goals, d_state, nullptr, nullptr, nullptr, nullptr);
+    else
+        exit_colors_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
+            *pool, (uint16_t *)d_board, (const uint16_t *)d_goals, d_state);
     SLB_LAUNCHED();
     return SLB_OK;
 }
 
-int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
                  slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
                  uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
                  void *stream) {
@@ -230,8 +321,9 @@ int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goa
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (fast_shape(pool->h, pool->w)) {
-        launch_env_rollout_fast(*pool, n, d_board, d_goals, d_state, d_actions, 1, time_limit, seed,
-                                env_id0, d_reward, d_done, auto_reset_stride, st);
+        res_env_rollout_kernel<<<RES_GRID(n), st>>>(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals,
+                                                   d_state, d_actions, 1, time_limit, seed, env_id0,
+                                                   d_reward, d_done, auto_reset_stride);
         SLB_LAUNCHED();
         return SLB_OK;
     }
@@ -240,14 +332,14 @@ int slb_env_step(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goa
         return fail(SLB_ERR_UNSUPPORTED, "fused env step needs the %dx%d board in shared memory",
                     pool->h, pool->w);
     if (int rc = allow_smem(env_step_generic_kernel, bytes)) return rc;
-    env_step_generic_kernel<<<n, GEN_THREADS, bytes, st>>>(*pool, d_board, d_goals, d_state, d_actions,
+    env_step_generic_kernel<<<n, GEN_THREADS, bytes, st>>>(*pool, (uint16_t *)d_board, (uint16_t *)d_goals, d_state, d_actions,
                                                           time_limit, seed, env_id0, d_reward,
                                                           d_done, auto_reset_stride);
     SLB_LAUNCHED();
     return SLB_OK;
 }
 
-int slb_env_rollout(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
                     slb_env_state *d_state, const uint8_t *d_actions, int t_steps, int time_limit,
                     uint64_t seed, uint64_t env_id0, int32_t *d_reward, uint8_t *d_done,
                     int auto_reset_stride, void *stream) {
@@ -256,9 +348,9 @@ int slb_env_rollout(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_
         return fail(SLB_ERR_INVALID, "slb_env_rollout: bad arguments");
     if (n == 0 || t_steps == 0) return SLB_OK;
     if (fast_shape(pool->h, pool->w)) {
-        launch_env_rollout_fast(*pool, n, d_board, d_goals, d_state, d_actions, t_steps, time_limit,
-                                seed, env_id0, d_reward, d_done, auto_reset_stride,
-                                (cudaStream_t)stream);
+        res_env_rollout_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(
+            *pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions, t_steps, time_limit,
+            seed, env_id0, d_reward, d_done, auto_reset_stride);
         SLB_LAUNCHED();
         return SLB_OK;
     }
@@ -272,7 +364,7 @@ int slb_env_rollout(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_
 }
 
 
-int slb_env_step_host(const slb_pool *pool, int n, uint16_t *d_board, uint16_t *d_goals,
+int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
                       uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                       int auto_reset_stride, void *stream) {
@@ -352,15 +444,36 @@ int slb_accumulate_stats(int n, const slb_env_state *d_state, const int32_t *d_r
     return SLB_OK;
 }
 
-int slb_get_obs(const slb_pool *pool, int n, const uint16_t *d_board, const uint16_t *d_goals,
+int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
                 const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
                 uint16_t *d_obs, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || vh < 1 || vw < 1 || !d_board || !d_goals || !d_state || !d_obs)
         return fail(SLB_ERR_INVALID, "slb_get_obs: bad arguments");
     if (n == 0) return SLB_OK;
-    get_obs_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool, d_board, d_goals, d_state, vh, vw,
-                                                               remove_white_goals, d_obs);
+    if (fast_shape(pool->h, pool->w))
+        res_obs_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(
+            *pool, n, (const uint32_t *)d_board, (const uint32_t *)d_goals, d_state, vh, vw,
+            remove_white_goals, d_obs);
+    else
+        get_obs_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
+            *pool, (const uint16_t *)d_board, (const uint16_t *)d_goals, d_state, vh, vw,
+            remove_white_goals, d_obs);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *d_channels, int n_channels,
+                     uint16_t *d_out, void *stream) {
+    if (!d_words || !d_channels || !d_out || n_channels < 1 || n_channels > 16)
+        return fail(SLB_ERR_INVALID, "slb_obs_channels: bad arguments");
+    if ((uintptr_t)d_out % 4) return fail(SLB_ERR_INVALID, "slb_obs_channels: d_out must be 4-byte aligned");
+    if (m == 0) return SLB_OK;
+    size_t pairs = (m * (size_t)n_channels + 1) / 2;
+    size_t blocks = (pairs + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    obs_channels_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_words, m, d_channels,
+                                                                         n_channels, d_out);
     SLB_LAUNCHED();
     return SLB_OK;
 }

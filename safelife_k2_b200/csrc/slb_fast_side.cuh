@@ -94,15 +94,17 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
     uint32_t A[16], C[16];
     load_planes(board0 + i * cells, stage, h, w, vec, A);
     load_planes(board1 + i * cells, stage, h, w, vec, C);
-    const uint64_t env = env_id0 + (uint64_t)i, thr = spawn_threshold(spawn_prob[i]);
+    const uint64_t env = env_id0 + (uint64_t)i;
+    const float thr = spawn_prob[i];
+    bool ch;
     uint64_t counter = counters ? counters[i] : 0;
     const int catch_up = num_steps[i];
-    for (int t = 0; t < catch_up; t++) counter = physics_planes(A, g, thr, seed, env, counter);  // :135-136
+    for (int t = 0; t < catch_up; t++) counter = physics_planes(A, g, thr, seed, env, counter, ch);  // :135-136
     int nkeys = 0;
     bool overflow = false;
     for (int t = 0; t < num_samples && !overflow; t++) {  // :137-141, the inaction board draws first
-        counter = physics_planes(A, g, thr, seed, env, counter);
-        counter = physics_planes(C, g, thr, seed, env, counter);
+        counter = physics_planes(A, g, thr, seed, env, counter, ch);
+        counter = physics_planes(C, g, thr, seed, env, counter, ch);
         se_accumulate_planes(A, g, 0, kmax, nplanes, nkeys, overflow, cnt, sel);
         se_accumulate_planes(C, g, 1, kmax, nplanes, nkeys, overflow, cnt, sel);
     }

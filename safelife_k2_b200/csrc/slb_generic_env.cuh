@@ -83,6 +83,35 @@ env_step_generic_kernel(slb_pool pool, uint16_t *board, uint16_t *goals, slb_env
 }
 
 // ---------------------------------------------------------------------------------------------
+// SafeLifeGame.advance_board alone (safelife_game.py:657-660) on uint16-resident state.  grid = N,
+// dynamic smem = h*w*2.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(GEN_THREADS)
+game_advance_generic_kernel(slb_pool pool, uint16_t *board, uint16_t *goals, slb_env_state *state,
+                            uint64_t seed, uint64_t env_id0) {
+    extern __shared__ uint16_t sm_cells[];
+    __shared__ int warp_tot[GEN_THREADS / 32];
+    const int i = blockIdx.x, h = pool.h, w = pool.w, cells = h * w;
+    uint16_t *b = board + (size_t)i * cells, *g = goals + (size_t)i * cells;
+    slb_env_state *st = state + i;
+    const uint64_t env = env_id0 + (uint64_t)i;
+    const uint64_t thr = spawn_threshold(pool.spawn_prob[st->level_id]);
+    uint64_t counter = st->rng_counter;
+    int d0 = 0, d1 = 0, d2 = 0;
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) sm_cells[c] = b[c];
+    __syncthreads();
+    counter = advance_pass<false>(sm_cells, b, h, w, thr, seed, env, counter, warp_tot, nullptr, d0, d1, d2);
+    __syncthreads();
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) sm_cells[c] = g[c];
+    __syncthreads();
+    counter = advance_pass<false>(sm_cells, g, h, w, thr, seed, env, counter, warp_tot, nullptr, d0, d1, d2);
+    if (threadIdx.x == 0) {
+        st->rng_counter = counter;
+        st->num_steps += 1;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // A13/A14: side_effect_score up to the EMD (side_effects.py:59-141).  grid = N episodes.
 // buf: 4 boards of h*w cells (b0 ping/pong, b1 ping/pong) in shared memory (USE_SMEM) or in the
 // caller's scratch.  Key table per episode in shared memory; count maps in global memory.

@@ -157,96 +157,108 @@ __device__ __forceinline__ void store_planes(uint16_t *__restrict__ dst, uint16_
 
 // ---------------------------------------------------------------------------------------------
 // One advance_board step on the planes (advance_board.c:34-120, closed form of Appendix A).
-// Returns the env's updated draw counter.
+// Returns the env's updated draw counter; `changed` (warp-uniform) says whether any cell changed.
+//
+// The evaluation is lazy but exact: the alive count n of every 3x3 is always computed; the flag
+// summaries (preserving / inhibiting / spawning), the draws and the colour inheritance are only
+// evaluated when some cell of this board can actually need them (all tests are warp votes, i.e.
+// per board).  A board on which nothing dies, nothing can be born and no spawner exists costs the
+// count and three votes.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g, uint64_t thr,
-                                                   uint64_t seed, uint64_t env, uint64_t counter) {
-    const uint32_t a = P[0];
-    const uint32_t d2 = P[3] | P[8];  // exit bit aliases destructible (advance_board.c:44-46)
-    // ---- vertical 3-row combination (rows r-1, r, r+1) ----
-#define SLB_UP(v) __shfl_sync(FULL, (v), g.up)
-#define SLB_DN(v) __shfl_sync(FULL, (v), g.dn)
-    uint32_t v0, v1;  // alive count of the column triple, 2 bits
-    {
-        uint32_t u = SLB_UP(a), d = SLB_DN(a);
-        v0 = xor3(a, u, d);
-        v1 = maj3(a, u, d);
-    }
-    uint32_t vfl[6];  // OR over the column triple: preserving, inhibiting, spawning, spawner colours r/g/b
-    {
-        const uint32_t src[6] = {P[5], P[6], P[7], P[7] & P[9], P[7] & P[10], P[7] & P[11]};
-#pragma unroll
-        for (int k = 0; k < 6; k++) vfl[k] = or3(src[k], SLB_UP(src[k]), SLB_DN(src[k]));
-    }
-    uint32_t f0[4], f1[4];  // count (2 bits) of alive cells carrying D2 / R / G / B in the column triple
-    {
-        const uint32_t src[4] = {a & d2, a & P[9], a & P[10], a & P[11]};
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            uint32_t u = SLB_UP(src[k]), d = SLB_DN(src[k]);
-            f0[k] = xor3(src[k], u, d);
-            f1[k] = maj3(src[k], u, d);
-        }
-    }
-#undef SLB_UP
-#undef SLB_DN
-    // ---- horizontal combination of the three column triples ----
+__device__ __forceinline__ uint32_t box_or(uint32_t x, const Geo &g) {  // OR over the 3x3, centre included
+    const uint32_t v = or3(x, __shfl_sync(FULL, x, g.up), __shfl_sync(FULL, x, g.dn));
+    return or3(from_left(v, g), v, from_right(v, g));
+}
+
+// ">= 2 of the alive cells in the 3x3 carry the flag" (pairwise AND accumulation of
+// advance_board.c:18,28 in closed form); src = alive & flag
+__device__ __forceinline__ uint32_t box_two(uint32_t src, const Geo &g) {
+    const uint32_t u = __shfl_sync(FULL, src, g.up), d = __shfl_sync(FULL, src, g.dn);
+    const uint32_t f0 = xor3(src, u, d), f1 = maj3(src, u, d);  // column count, 2 bits
+    const uint32_t hi = or3(from_left(f1, g), f1, from_right(f1, g));
+    return hi | maj3(from_left(f0, g), f0, from_right(f0, g));
+}
+
+__device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g, float spawn_prob,
+                                                   uint64_t seed, uint64_t env, uint64_t counter,
+                                                   bool &changed) {
+    changed = false;
+    const uint32_t a = P[0], fz = P[4], sp = P[7];
+    // ---- alive count of the 3x3 (centre included): n = s0 + 2 n1 + 4 n2 (+ 8), n <= 9 ----
     uint32_t is3, is4;
     {
-        uint32_t l0 = from_left(v0, g), r0 = from_right(v0, g);
-        uint32_t l1 = from_left(v1, g), r1 = from_right(v1, g);
-        uint32_t s0 = xor3(l0, v0, r0), c0 = maj3(l0, v0, r0);
-        uint32_t s1 = xor3(l1, v1, r1), c1 = maj3(l1, v1, r1);
-        uint32_t n1 = c0 ^ s1, k = c0 & s1, n2 = c1 ^ k;  // n = s0 + 2 n1 + 4 n2 + 8 (c1 & k), n <= 9
+        const uint32_t u = __shfl_sync(FULL, a, g.up), d = __shfl_sync(FULL, a, g.dn);
+        const uint32_t v0 = xor3(a, u, d), v1 = maj3(a, u, d);
+        const uint32_t l0 = from_left(v0, g), r0 = from_right(v0, g);
+        const uint32_t l1 = from_left(v1, g), r1 = from_right(v1, g);
+        const uint32_t s0 = xor3(l0, v0, r0), c0 = maj3(l0, v0, r0);
+        const uint32_t s1 = xor3(l1, v1, r1), c1 = maj3(l1, v1, r1);
+        const uint32_t n1 = c0 ^ s1, k = c0 & s1, n2 = c1 ^ k;
         is3 = s0 & n1 & ~n2;
         is4 = ~s0 & ~n1 & n2;  // n2 set implies the 8s bit (c1 & k) is clear
     }
-    uint32_t fl[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) fl[k] = or3(from_left(vfl[k], g), vfl[k], from_right(vfl[k], g));
-    uint32_t two[4];  // ">= 2 alive cells in the 3x3 carry the flag"
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        uint32_t hi = or3(from_left(f1[k], g), f1[k], from_right(f1[k], g));
-        two[k] = hi | maj3(from_left(f0[k], g), f0[k], from_right(f0[k], g));
+    const uint32_t die0 = a & ~(fz | is3 | is4);       // dies unless preserved
+    const uint32_t open0 = ~(a | fz) & g.wmask;        // dead and not frozen
+    const uint32_t birth0 = open0 & is3;               // born unless inhibited
+    if (!__any_sync(FULL, (die0 | birth0 | sp) != 0)) return counter;  // fixed point, no spawner
+    // ---- flag summaries: taken from every cell of the 3x3, alive or not ----
+    uint32_t PR = 0, IH = 0;
+    if (__any_sync(FULL, (P[5] | P[6]) != 0)) {
+        PR = box_or(P[5], g);
+        IH = box_or(P[6], g);
     }
-    const uint32_t PR = fl[0], IH = fl[1], SP = fl[2];
-    const uint32_t tR = two[1] | fl[3], tG = two[2] | fl[4], tB = two[3] | fl[5];
-    // ---- rule ----
-    const uint32_t fz = P[4];
-    const uint32_t die = a & ~(fz | PR | is3 | is4);
-    const uint32_t open = ~a & ~(fz | IH) & g.wmask;  // dead, not frozen, not inhibited
+    const uint32_t die = die0 & ~PR;
+    const uint32_t open = open0 & ~IH;
     const uint32_t birth = open & is3;
-    const uint32_t elig = open & ~is3 & SP;  // the cells that consume a draw (advance_board.c:110)
+    const bool any_sp = __any_sync(FULL, sp != 0);
     uint32_t spawn = 0;
-    if (__any_sync(FULL, elig != 0)) {
-        // raster-order rank of every eligible cell: exclusive prefix over rows, then within the row
-        int cnt = __popc(elig), incl = cnt;
-        const int lane = threadIdx.x & 31;
+    if (any_sp) {
+        const uint32_t elig = open & ~is3 & box_or(sp, g);  // the cells that consume a draw (:110)
+        if (__any_sync(FULL, elig != 0)) {
+            // raster-order rank of every eligible cell: exclusive prefix over rows, then in the row
+            const uint64_t thr = spawn_threshold(spawn_prob);
+            int cnt = __popc(elig), incl = cnt;
+            const int lane = threadIdx.x & 31;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            int t = __shfl_up_sync(FULL, incl, o);
-            if (lane >= o) incl += t;
+            for (int o = 1; o < 32; o <<= 1) {
+                int t = __shfl_up_sync(FULL, incl, o);
+                if (lane >= o) incl += t;
+            }
+            uint64_t base = counter + (uint64_t)(incl - cnt);
+            uint32_t e = elig;
+            while (e) {
+                uint32_t bit = e & (0u - e);
+                e ^= bit;
+                if (stream_u53(seed, env, base) < thr) spawn |= bit;
+                base++;
+            }
+            counter += (uint64_t)__shfl_sync(FULL, incl, 31);
         }
-        uint64_t base = counter + (uint64_t)(incl - cnt);
-        uint32_t e = elig;
-        while (e) {
-            uint32_t bit = e & (0u - e);
-            e ^= bit;
-            if (stream_u53(seed, env, base) < thr) spawn |= bit;
-            base++;
-        }
-        counter += (uint64_t)__shfl_sync(FULL, incl, 31);
     }
     const uint32_t born = birth | spawn;
-    const uint32_t keep = ~(die | born);
+    uint32_t nD = 0, nR = 0, nG = 0, nB = 0;
+    if (__any_sync(FULL, born != 0)) {
+        // inherited bits: present in >= 2 alive cells of the 3x3; D2 = destructible | exit (:44-46)
+        nD = (birth & box_two(a & (P[3] | P[8]), g)) | spawn;  // spawned cells are always destructible
+        uint32_t tR = box_two(a & P[9], g), tG = box_two(a & P[10], g), tB = box_two(a & P[11], g);
+        if (any_sp) {  // colour of ANY spawning cell in the 3x3, alive or not (:19)
+            tR |= box_or(sp & P[9], g);
+            tG |= box_or(sp & P[10], g);
+            tB |= box_or(sp & P[11], g);
+        }
+        nR = born & tR; nG = born & tG; nB = born & tB;
+    }
+    const uint32_t flip = die | born;
+    if (!__any_sync(FULL, flip != 0)) return counter;
+    changed = true;
+    const uint32_t keep = ~flip;
 #pragma unroll
     for (int b = 0; b < 16; b++) P[b] &= keep;  // killed cells lose everything; births discard residue
     P[0] |= born;
-    P[3] |= (birth & two[0]) | spawn;  // spawned cells are always destructible
-    P[9] |= born & tR;
-    P[10] |= born & tG;
-    P[11] |= born & tB;
+    P[3] |= nD;
+    P[9] |= nR;
+    P[10] |= nG;
+    P[11] |= nB;
     return counter;
 }
 

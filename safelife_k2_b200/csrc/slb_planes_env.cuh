@@ -4,90 +4,125 @@
 
 namespace slb {
 
-__device__ __forceinline__ uint32_t bit_at(uint32_t plane, int lane_y, int x) {
-    return (__shfl_sync(FULL, plane, lane_y) >> x) & 1u;
-}
-
 // ---------------------------------------------------------------------------------------------
 // execute_action on planes (safelife_game.py:347-393, move_agent :308-345).
 // Requires H >= 4 and W >= 4 so that the agent cell A, front F, two-ahead F2 and behind B are four
 // distinct cells (smaller boards alias F2 and B and take the literal generic path instead).
 // All reads see the pre-action board, which is what the reference reads too: the pull test on B
 // happens after the moves, but no move writes B.  Warp-uniform control flow (one env per warp).
-// Returns the action reward; updates ax, ay, orientation, game_over.
+// Returns the action reward; updates ax, ay, orientation, game_over; `touched` (warp-uniform) says
+// whether the board was written.
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t bit_of(uint32_t plane, int x) { return (plane >> x) & 1u; }
+
 __device__ __forceinline__ int action_planes(uint32_t P[16], const Geo &g, int &ax, int &ay,
                                              int &orientation, int &game_over, int action,
-                                             int can_exit) {
+                                             int can_exit, bool &touched) {
+    touched = false;
     if (game_over || action < 1 || action > 8) return 0;
     const int lane = threadIdx.x & 31;
     const int dir = (action - 1) & 3;
     orientation = dir;
     const int fx = (dir == 1) - (dir == 3), fy = (dir == 2) - (dir == 0);
     const int h = g.h, w = g.w;
-    const int xF = (ax + fx + w) % w, yF = (ay + fy + h) % h;
+    int xF = ax + fx, yF = ay + fy;
+    xF = xF < 0 ? w - 1 : (xF >= w ? 0 : xF);
+    yF = yF < 0 ? h - 1 : (yF >= h ? 0 : yF);
     uint32_t nz = 0;
 #pragma unroll
     for (int b = 0; b < 16; b++) nz |= P[b];
-    const uint32_t f_nz = bit_at(nz, yF, xF);
+    // front cell summary, extracted by its row's lane: bit0 non-empty, 1 exit, 2 pushable, 3 destructible
+    uint32_t sF = bit_of(nz, xF) | (bit_of(P[8], xF) << 1) | (bit_of(P[2], xF) << 2) | (bit_of(P[3], xF) << 3);
+    sF = __shfl_sync(FULL, sF, yF);
     if (action >= 5) {  // TOGGLE
-        if (!f_nz) {
+        if (!(sF & 1u)) {
             // empty -> life | player colour (alive | destructible | colour of the agent cell)
+            uint32_t cA = bit_of(P[9], ax) | (bit_of(P[10], ax) << 1) | (bit_of(P[11], ax) << 2);
+            cA = __shfl_sync(FULL, cA, ay);
             const uint32_t m = (lane == yF) ? (1u << xF) : 0u;
             P[0] |= m;
             P[3] |= m;
-#pragma unroll
-            for (int b = 9; b <= 11; b++)
-                if (bit_at(P[b], ay, ax)) P[b] |= m;
-        } else if (bit_at(P[3], yF, xF)) {  // destructible -> empty
+            if (cA & 1u) P[9] |= m;
+            if (cA & 2u) P[10] |= m;
+            if (cA & 4u) P[11] |= m;
+            touched = true;
+        } else if (sF & 8u) {  // destructible -> empty
             const uint32_t k = (lane == yF) ? ~(1u << xF) : 0xffffffffu;
 #pragma unroll
             for (int b = 0; b < 16; b++) P[b] &= k;
+            touched = true;
         }
         return 0;
     }
     // MOVE
-    const int xB = (ax - fx + w) % w, yB = (ay - fy + h) % h;
-    const int xF2 = (ax + 2 * fx + 2 * w) % w, yF2 = (ay + 2 * fy + 2 * h) % h;
     bool moved = false, push = false;
     int reward = 0;
-    if (!f_nz) {
+    int xF2 = xF, yF2 = yF;
+    if (!(sF & 1u)) {
         moved = true;
-    } else if (bit_at(P[8], yF, xF) && can_exit) {
+    } else if ((sF & 2u) && can_exit) {
         game_over = 1;
         reward = 1;
-    } else if (bit_at(P[2], yF, xF)) {
-        if (!bit_at(nz, yF2, xF2)) {
+    } else if (sF & 4u) {
+        xF2 = xF + fx; yF2 = yF + fy;
+        xF2 = xF2 < 0 ? w - 1 : (xF2 >= w ? 0 : xF2);
+        yF2 = yF2 < 0 ? h - 1 : (yF2 >= h ? 0 : yF2);
+        uint32_t s2 = bit_of(nz, xF2) | (bit_of(P[8], xF2) << 1);
+        s2 = __shfl_sync(FULL, s2, yF2);
+        if (!(s2 & 1u)) {
             moved = true;
             push = true;  // the pushed cell moves on to F2
-        } else if (bit_at(P[8], yF2, xF2)) {
+        } else if (s2 & 2u) {
             moved = true;  // pushed out of the level: F is simply overwritten by the agent
         }
     }
     if (!moved) return reward;
-    const bool pull = bit_at(P[15], yB, xB) != 0;
-    // Every written cell takes the value of its predecessor along the direction of motion:
-    //   F <- A always; F2 <- F when pushing; A <- B when pulling (else A <- 0; B <- 0 when pulling).
-    uint32_t set_m = 0, clr_m = 0;  // this lane's destination bits that receive / are cleared
-    if (lane == yF) { set_m |= 1u << xF; }
-    if (push && lane == yF2) { set_m |= 1u << xF2; }
-    if (lane == ay) { if (pull) set_m |= 1u << ax; else clr_m |= 1u << ax; }
-    if (pull && lane == yB) { clr_m |= 1u << xB; }
-    const uint32_t keep = ~(set_m | clr_m);
+    touched = true;
+    int xB = ax - fx, yB = ay - fy;
+    xB = xB < 0 ? w - 1 : (xB >= w ? 0 : xB);
+    yB = yB < 0 ? h - 1 : (yB >= h ? 0 : yB);
+    const bool pull = (__shfl_sync(FULL, P[15], yB) >> xB) & 1u;
+    // Every moving cell advances one step along the direction of motion: A -> F always, F -> F2 when
+    // pushing, B -> A when pulling.  src_m: this lane's cells that move; all of them are vacated,
+    // and each destination receives its predecessor (a pushed-out cell's old place F receives A).
+    uint32_t src_m = 0;
+    if (lane == ay) src_m |= 1u << ax;
+    if (push && lane == yF) src_m |= 1u << xF;
+    if (pull && lane == yB) src_m |= 1u << xB;
+    uint32_t dst_m;  // this lane's cells that receive a value
     if (fy == 0) {
-        // horizontal: predecessor is the cell one step back along x in the same row
+        // horizontal: every moving cell lies in row ay; one step along x, toroidal within W bits
+        const int sh = fx > 0 ? 1 : 31;  // rotate-left amount in a 32-bit word
+        const int fix = fx > 0 ? w : 32 - w;  // where a bit that left the W-bit field reappears
+        const bool wrap = (w < 32) && (fx > 0 ? (src_m >> (w - 1)) & 1u : src_m & 1u);
+        const bool any_wrap = __any_sync(FULL, wrap);
+        dst_m = __funnelshift_l(src_m, src_m, sh);
+        if (any_wrap) dst_m = (dst_m & g.wmask) | ((dst_m & ~g.wmask) >> fix);
+        const uint32_t keep = ~(src_m | dst_m);
+        if (!any_wrap) {
 #pragma unroll
-        for (int b = 0; b < 16; b++) {
-            uint32_t pred = (fx > 0) ? from_left(P[b], g) : from_right(P[b], g);
-            P[b] = (P[b] & keep) | (pred & set_m);
+            for (int b = 0; b < 16; b++) {
+                const uint32_t t = P[b] & src_m;
+                P[b] = (P[b] & keep) | __funnelshift_l(t, t, sh);
+            }
+        } else {
+#pragma unroll
+            for (int b = 0; b < 16; b++) {
+                uint32_t t = P[b] & src_m;
+                t = __funnelshift_l(t, t, sh);
+                t = (t & g.wmask) | ((t & ~g.wmask) >> fix);
+                P[b] = (P[b] & keep) | t;
+            }
         }
     } else {
-        // vertical: predecessor is the same column in the row one step back along y
-        const int src = g.row ? ((fy > 0) ? g.up : g.dn) : lane;
+        // vertical: same column, the value comes from the row one step back along y
+        const int from = g.row ? ((fy > 0) ? g.up : g.dn) : lane;
+        dst_m = __shfl_sync(FULL, src_m, from);
+        const uint32_t keep = ~(src_m | dst_m);
 #pragma unroll
         for (int b = 0; b < 16; b++) {
-            uint32_t pred = __shfl_sync(FULL, P[b], src);
-            P[b] = (P[b] & keep) | (pred & set_m);
+            const uint32_t t = __shfl_sync(FULL, P[b] & src_m, from);
+            P[b] = (P[b] & keep) | t;
         }
     }
     ax = xF;

@@ -1,0 +1,449 @@
+// slb_resident.cuh — the RESIDENT env state of boards with 4 <= H, W <= 32 (the 26x26 benchmark
+// levels) and the kernels that step it: one warp per env, board and goals as 16 bit-planes in
+// registers (lane = row, bit = column), loaded from and stored to HBM *already bit-sliced*, so a
+// step has no cell<->plane transposition and no shared-memory staging at all.
+//
+// Resident layout of one board (64*H bytes, see slb_resident_bytes): 4 plane groups x H rows x
+// uint4; group g, row r is the uint4 at index g*H + r and holds the row's words of 4 planes:
+//     group 0: alive(0) frozen(4) red(9) green(10)        group 2: agent(1) preserving(5) inhibiting(6) exit(8)
+//     group 1: blue(11) destructible(3) pushable(2) pullable(15)   group 3: spawning(7) bits 12, 13, 14
+// A warp reads a group with one fully coalesced 16-byte load per lane.  Groups 2 and 3 are only
+// read / written when some board of the pool (or an imported board) has one of their bits: the
+// pool keeps an OR of every cell it has seen (pool.plane_bits); a group outside it is all-zero in
+// memory (buffers start zeroed) and stays so, because no rule creates a bit that no cell has,
+// except births (bits 0, 3, 9-11: groups 0/1, always present) and exit painting (bits 4, 8, 9 —
+// only where an exit cell, which has bit 8, exists).
+//
+// The uint16 [N,H,W] cell layout of the reference stays the format of every API boundary
+// (slb_resident_import / slb_resident_export, slb_advance_board, the level pool, observations).
+#pragma once
+#include "slb_planes_env.cuh"
+
+namespace slb {
+
+constexpr int RES_WARPS = 4;  // warps (= envs) per CTA
+
+inline bool fast_shape(int h, int w) { return h >= 4 && w >= 4 && h <= 32 && w <= 32; }
+
+__host__ __device__ inline size_t resident_words(int h) { return (size_t)16 * h; }
+
+// which groups a plane-bit mask touches (bit g set = group g present); groups 0/1 always
+__host__ __device__ inline unsigned groups_of(uint32_t plane_bits) {
+    unsigned gm = 3u;
+    if (plane_bits & ((1u << 1) | (1u << 5) | (1u << 6) | (1u << 8))) gm |= 4u;
+    if (plane_bits & ((1u << 7) | (7u << 12))) gm |= 8u;
+    return gm;
+}
+
+__device__ __forceinline__ void load_res(const uint32_t *__restrict__ base, const Geo &g,
+                                         unsigned groups, uint32_t P[16]) {
+    const int lane = threadIdx.x & 31;
+    const uint4 *b4 = reinterpret_cast<const uint4 *>(base);
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    const uint4 q0 = g.row ? b4[lane] : z;
+    const uint4 q1 = g.row ? b4[g.h + lane] : z;
+    const uint4 q2 = (g.row && (groups & 4u)) ? b4[2 * g.h + lane] : z;
+    const uint4 q3 = (g.row && (groups & 8u)) ? b4[3 * g.h + lane] : z;
+    P[0] = q0.x; P[4] = q0.y; P[9] = q0.z; P[10] = q0.w;
+    P[11] = q1.x; P[3] = q1.y; P[2] = q1.z; P[15] = q1.w;
+    P[1] = q2.x; P[5] = q2.y; P[6] = q2.z; P[8] = q2.w;
+    P[7] = q3.x; P[12] = q3.y; P[13] = q3.z; P[14] = q3.w;
+}
+
+__device__ __forceinline__ void store_res(uint32_t *__restrict__ base, const Geo &g, unsigned groups,
+                                          const uint32_t P[16]) {
+    const int lane = threadIdx.x & 31;
+    if (!g.row) return;
+    uint4 *b4 = reinterpret_cast<uint4 *>(base);
+    b4[lane] = make_uint4(P[0], P[4], P[9], P[10]);
+    b4[g.h + lane] = make_uint4(P[11], P[3], P[2], P[15]);
+    if (groups & 4u) b4[2 * g.h + lane] = make_uint4(P[1], P[5], P[6], P[8]);
+    if (groups & 8u) b4[3 * g.h + lane] = make_uint4(P[7], P[12], P[13], P[14]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Env scalars in registers (warp-uniform).  The 64-byte slb_env_state record moves as 4 x 16 B.
+// ---------------------------------------------------------------------------------------------
+struct EnvRegs {
+    int ax, ay, orientation, game_over, num_steps, level, ep_len, ep_done;
+    int old_points, can_exit, completed, possible;
+    long long ep_reward;
+    uint64_t counter;
+};
+
+__device__ __forceinline__ EnvRegs load_env(const slb_env_state *s) {
+    const uint4 *q = reinterpret_cast<const uint4 *>(s);
+    const uint4 a = q[0], b = q[1], c = q[2], d = q[3];
+    EnvRegs e;
+    e.ax = (int)a.x; e.ay = (int)a.y; e.orientation = (int)a.z; e.game_over = (int)a.w;
+    e.num_steps = (int)b.x; e.level = (int)b.y; e.ep_len = (int)b.z; e.ep_done = (int)b.w;
+    e.old_points = (int)c.x; e.can_exit = (int)c.y; e.completed = (int)c.z; e.possible = (int)c.w;
+    e.ep_reward = (long long)(((uint64_t)d.y << 32) | d.x);
+    e.counter = ((uint64_t)d.w << 32) | d.z;
+    return e;
+}
+
+__device__ __forceinline__ void store_env(slb_env_state *s, const EnvRegs &e) {
+    uint4 *q = reinterpret_cast<uint4 *>(s);
+    q[0] = make_uint4((uint32_t)e.ax, (uint32_t)e.ay, (uint32_t)e.orientation, (uint32_t)e.game_over);
+    q[1] = make_uint4((uint32_t)e.num_steps, (uint32_t)e.level, (uint32_t)e.ep_len, (uint32_t)e.ep_done);
+    q[2] = make_uint4((uint32_t)e.old_points, (uint32_t)e.can_exit, (uint32_t)e.completed, (uint32_t)e.possible);
+    q[3] = make_uint4((uint32_t)(uint64_t)e.ep_reward, (uint32_t)((uint64_t)e.ep_reward >> 32),
+                      (uint32_t)e.counter, (uint32_t)(e.counter >> 32));
+}
+
+struct LevelConsts {
+    float spawn_prob;
+    int baseline;
+    double min_perf;
+    uint32_t e0;  // this lane's row of the level's initial exit cells
+};
+
+__device__ __forceinline__ LevelConsts load_level(const slb_pool &pool, int level, const Geo &g) {
+    LevelConsts c;
+    const int lane = threadIdx.x & 31;
+    c.spawn_prob = pool.spawn_prob[level];
+    c.baseline = pool.baseline[level];
+    c.min_perf = pool.min_performance[level];
+    c.e0 = g.row ? pool.exit_mask[(size_t)level * g.h + lane] : 0u;
+    return c;
+}
+
+// score -> completed / possible / can_exit (safelife_game.py:522-526, 601-631), then repaint the
+// exits (:531-537).  Returns current_points of the board BEFORE repainting (exit cells are dead
+// either way, so the value is the same after it).
+__device__ __forceinline__ int score_and_paint(uint32_t B[16], const uint32_t G[16], const Geo &g,
+                                               const LevelConsts &lc, EnvRegs &e, bool paint) {
+    const RowScore rs = score_planes(B, G, g);
+    const int pts = warp_sum(rs.points), cur = warp_sum(rs.current), pos = warp_sum(rs.possible);
+    e.completed = cur - lc.baseline;
+    e.possible = pos - lc.baseline;
+    e.can_exit = can_exit_rule(lc.min_perf, e.completed, e.possible);
+    if (paint) paint_exits(B, lc.e0, e.can_exit);
+    return pts;
+}
+
+// reset from the pool's resident level copies (safelife_env.py:188-198); every lane calls
+__device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, const Geo &g,
+                                              unsigned gb, unsigned gg, uint32_t B[16], uint32_t G[16],
+                                              LevelConsts &lc, EnvRegs &e) {
+    const size_t words = resident_words(g.h);
+    load_res((const uint32_t *)pool.board_res + level * words, g, gb, B);
+    load_res((const uint32_t *)pool.goals_res + level * words, g, gg, G);
+    lc = load_level(pool, level, g);
+    score_and_paint(B, G, g, lc, e, true);
+    // _old_game_value is taken AFTER update_exit_colors (safelife_env.py:190-192): re-score, an
+    // exit cell that was alive in the level record is dead once painted
+    e.old_points = warp_sum(score_planes(B, G, g).points);
+    e.ax = pool.agent_x[level]; e.ay = pool.agent_y[level]; e.orientation = pool.orientation[level];
+    e.game_over = 0; e.num_steps = 0; e.level = level; e.ep_len = 0; e.ep_done = 0; e.ep_reward = 0;
+    // e.counter deliberately untouched: the stream keeps running across episodes
+}
+
+// ---------------------------------------------------------------------------------------------
+// A12 fused: T env steps per launch (T = 1 with a policy in the loop); board + goals stay in
+// registers between steps.  grid = ceil(N / RES_WARPS).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RES_WARPS * 32, 7)
+res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
+                       const uint8_t *__restrict__ actions, int t_steps, int time_limit,
+                       uint64_t seed, uint64_t env_id0, int32_t *reward_out, uint8_t *done_out,
+                       int auto_reset_stride) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const size_t words = resident_words(g.h);
+    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    uint32_t *bp = board + i * words, *gp = goals + i * words;
+    uint32_t B[16], G[16];
+    load_res(bp, g, gb, B);
+    load_res(gp, g, gg, G);
+    EnvRegs e = load_env(state + i);
+    int action = actions[i];
+    LevelConsts lc = load_level(pool, e.level, g);
+    const uint64_t env = env_id0 + (uint64_t)i;
+    bool g_dirty = false;
+
+    for (int t = 0; t < t_steps; t++) {
+        const int next_action = (t + 1 < t_steps) ? actions[(size_t)(t + 1) * n + i] : 0;
+        bool touched, ch;
+        int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched);
+        // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
+        e.num_steps += 1;
+        e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch);
+        e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch);
+        g_dirty |= ch;
+        const int pts = score_and_paint(B, G, g, lc, e, true);
+        reward += pts - e.old_points;
+        e.old_points = pts;
+        e.ep_len += 1;
+        e.ep_reward += reward;
+        const int done = (e.ep_len > time_limit) || e.game_over;
+        e.ep_done = done;
+        if (lane == 0) {
+            if (reward_out) reward_out[(size_t)t * n + i] = reward;
+            if (done_out) done_out[(size_t)t * n + i] = (uint8_t)done;
+        }
+        if (done && auto_reset_stride > 0) {
+            reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, gb, gg, B, G, lc, e);
+            g_dirty = true;
+        }
+        action = next_action;
+    }
+    store_res(bp, g, gb, B);
+    if (g_dirty) store_res(gp, g, gg, G);
+    if (lane == 0) store_env(state + i, e);
+}
+
+// ---------------------------------------------------------------------------------------------
+// The single stages as their own launches (the SafeLifeGame methods call them one by one).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_reset_kernel(slb_pool pool, int n, const int32_t *__restrict__ level_ids,
+                 const uint8_t *__restrict__ mask, uint32_t *board, uint32_t *goals,
+                 slb_env_state *state) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i >= n || (mask && !mask[i])) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const size_t words = resident_words(g.h);
+    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    uint32_t B[16], G[16];
+    LevelConsts lc;
+    EnvRegs e = load_env(state + i);
+    reset_env_res(pool, level_ids[i], g, gb, gg, B, G, lc, e);
+    store_res(board + i * words, g, gb, B);
+    store_res(goals + i * words, g, gg, G);
+    if (lane == 0) store_env(state + i, e);
+}
+
+// execute_action alone (safelife_game.py:347-393)
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_action_kernel(slb_pool pool, int n, uint32_t *board, slb_env_state *state,
+                  const uint8_t *__restrict__ actions, int32_t *reward_out) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const unsigned gb = groups_of(pool.plane_bits[0]);
+    uint32_t *bp = board + i * resident_words(g.h);
+    uint32_t B[16];
+    load_res(bp, g, gb, B);
+    EnvRegs e = load_env(state + i);
+    bool touched;
+    const int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, actions[i], e.can_exit, touched);
+    if (touched) store_res(bp, g, gb, B);
+    if (lane == 0) {
+        store_env(state + i, e);
+        if (reward_out) reward_out[i] = reward;
+    }
+}
+
+// SafeLifeGame.advance_board alone (safelife_game.py:657-660): num_steps += 1, board then goals
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_advance_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
+                   uint64_t seed, uint64_t env_id0) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const size_t words = resident_words(g.h);
+    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    uint32_t P[16];
+    EnvRegs e = load_env(state + i);
+    const float p = pool.spawn_prob[e.level];
+    const uint64_t env = env_id0 + (uint64_t)i;
+    bool ch;
+    load_res(board + i * words, g, gb, P);
+    e.counter = physics_planes(P, g, p, seed, env, e.counter, ch);
+    if (ch) store_res(board + i * words, g, gb, P);
+    load_res(goals + i * words, g, gg, P);
+    e.counter = physics_planes(P, g, p, seed, env, e.counter, ch);
+    if (ch) store_res(goals + i * words, g, gg, P);
+    e.num_steps += 1;
+    if (lane == 0) store_env(state + i, e);
+}
+
+// current_points / performance_ratio / can_exit (read-only), or update_exit_colors (PAINT)
+template <bool PAINT>
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_score_kernel(slb_pool pool, int n, uint32_t *board, const uint32_t *goals, slb_env_state *state,
+                 int32_t *points, int32_t *completed, int32_t *possible, uint8_t *can_exit) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const size_t words = resident_words(g.h);
+    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    uint32_t B[16], G[16];
+    load_res(board + i * words, g, gb, B);
+    load_res(goals + i * words, g, gg, G);
+    EnvRegs e = load_env(state + i);
+    const LevelConsts lc = load_level(pool, e.level, g);
+    const int pts = score_and_paint(B, G, g, lc, e, PAINT);
+    if (PAINT) {
+        store_res(board + i * words, g, gb, B);
+        if (lane == 0) store_env(state + i, e);
+    } else if (lane == 0) {
+        if (points) points[i] = pts;
+        if (completed) completed[i] = e.completed;
+        if (possible) possible[i] = e.possible;
+        if (can_exit) can_exit[i] = (uint8_t)e.can_exit;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// cells <-> resident planes (API boundary).  The import ORs every cell it sees into *plane_bits.
+// ---------------------------------------------------------------------------------------------
+constexpr int RES_STAGE_U16 = 32 * 34;  // per-warp staging area (H <= 32 rows, stride <= 34)
+
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_import_kernel(const uint16_t *__restrict__ cells, uint32_t *planes, int n, int h, int w,
+                  uint32_t *plane_bits, bool vec) {
+    __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + warp;
+    if (i >= n) return;
+    const Geo g = make_geo(h, w);
+    uint32_t P[16];
+    load_planes(cells + (size_t)i * h * w, stage[warp], h, w, vec, P);
+    store_res(planes + i * resident_words(h), g, 15u, P);
+    if (plane_bits) {
+        uint32_t bits = 0;
+#pragma unroll
+        for (int b = 0; b < 16; b++) bits |= (P[b] != 0u) ? (1u << b) : 0u;
+        bits = __reduce_or_sync(FULL, bits);
+        if (lane == 0 && (bits & ~*plane_bits)) atomicOr(plane_bits, bits);
+    }
+}
+
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_export_kernel(const uint32_t *__restrict__ planes, uint16_t *cells, int n, int h, int w, bool vec) {
+    __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
+    const int warp = threadIdx.x >> 5;
+    const int i = blockIdx.x * RES_WARPS + warp;
+    if (i >= n) return;
+    const Geo g = make_geo(h, w);
+    uint32_t P[16];
+    load_res(planes + i * resident_words(h), g, 15u, P);
+    store_planes(cells + (size_t)i * h * w, stage[warp], h, w, vec, P);
+}
+
+// ---------------------------------------------------------------------------------------------
+// get_obs (safelife_env.py:125-155) + recenter_view (helper_utils.py:41-74) from resident planes.
+// out[i][vy][vx] = (board + ((goals & colours, white removed) << 3)) cropped toroidally around the
+// agent; exit cells of the INITIAL board that fall outside the view are clamped onto its rim, in
+// raster order of the exit cells (later ones overwrite earlier ones, like the fancy assignment).
+// The combined board is formed on the planes, transposed once into a per-warp shared image of
+// uint16 cells, and gathered from there (any view size, also views larger than the board).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int pymod_w(int a, int m) {
+    int r = a % m;
+    return r < 0 ? r + m : r;
+}
+
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
+               const uint32_t *__restrict__ goals, const slb_env_state *__restrict__ state, int vh,
+               int vw, int remove_white, uint16_t *obs) {
+    __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + warp;
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const int h = g.h, w = g.w, S = row_stride(w);
+    const size_t words = resident_words(h);
+    uint32_t O[16], G[16];
+    load_res(board + i * words, g, groups_of(pool.plane_bits[0]), O);
+    load_res(goals + i * words, g, 3u, G);  // only the colour planes (groups 0/1) are needed
+    {
+        uint32_t cr = G[9], cg = G[10], cb = G[11];
+        if (remove_white) {
+            const uint32_t nw = ~(cr & cg & cb);
+            cr &= nw; cg &= nw; cb &= nw;
+        }
+        // uint16 add of (goal colours << 3) onto the board word: ripple through bits 12..15
+        uint32_t c = O[12] & cr;
+        O[12] ^= cr;
+        uint32_t t = O[13] ^ cg;
+        const uint32_t c2 = (O[13] & cg) | (t & c);
+        O[13] = t ^ c;
+        t = O[14] ^ cb;
+        c = (O[14] & cb) | (t & c2);
+        O[14] = t ^ c2;
+        O[15] ^= c;
+    }
+    uint16_t *sm = stage[warp];
+    {
+        uint32_t x[16];
+        planes_to_cells(O, x);
+        __syncwarp();
+        uint32_t *row = reinterpret_cast<uint32_t *>(sm) + lane * (S >> 1);
+#pragma unroll
+        for (int j = 0; j < 16; j++)
+            if (lane < h && 2 * j < w) row[j] = x[j];
+        __syncwarp();
+    }
+    const slb_env_state *st = state + i;
+    const int x0 = st->agent_x, y0 = st->agent_y, level = st->level_id;
+    const int x1 = x0 - vw / 2, y1 = y0 - vh / 2;
+    uint16_t *o = obs + (size_t)i * vh * vw;
+    int vy = 0, vx = lane;  // (vy, vx) of flat index k = lane, advanced by 32 per iteration
+    while (vx >= vw) { vx -= vw; vy++; }
+    int sy = pymod_w(y1 + vy, h), sx = pymod_w(x1 + vx, w);
+    for (int k = lane; k < vh * vw; k += 32) {
+        o[k] = sm[sy * S + sx];
+        vx += 32;
+        while (vx >= vw) { vx -= vw; vy++; }
+        sy = pymod_w(y1 + vy, h);
+        sx = pymod_w(x1 + vx, w);
+    }
+    __syncwarp();
+    // move_to_perimeter: every initial exit cell, raster order
+    const uint32_t e0 = g.row ? pool.exit_mask[(size_t)level * h + lane] : 0u;
+    unsigned rows = __ballot_sync(FULL, e0 != 0u);
+    while (rows) {
+        const int y = __ffs(rows) - 1;
+        rows &= rows - 1;
+        uint32_t m = __shfl_sync(FULL, e0, y);
+        while (m) {
+            const int x = __ffs(m) - 1;
+            m &= m - 1;
+            int jy = pymod_w(y - y0 + h / 2, h) - h / 2;
+            int jx = pymod_w(x - x0 + w / 2, w) - w / 2;
+            jy = min(max(jy + vh / 2, 0), vh - 1);
+            jx = min(max(jx + vw / 2, 0), vw - 1);
+            if (lane == 0) o[jy * vw + jx] = sm[y * S + x];
+        }
+    }
+}
+
+// packed observation words [M] -> boolean channels [M, C] uint16 (safelife_env.py:152-154):
+// out[m*C + c] = (words[m] >> channels[c]) & 1.  Flat over 32-bit output words, any alignment of M*C.
+__global__ void __launch_bounds__(256)
+obs_channels_kernel(const uint16_t *__restrict__ words, size_t m_words, const uint8_t *__restrict__ channels,
+                    int n_channels, uint16_t *out) {
+    __shared__ uint8_t ch[16];
+    if (threadIdx.x < 16) ch[threadIdx.x] = threadIdx.x < n_channels ? channels[threadIdx.x] : 0;
+    __syncthreads();
+    const size_t total = m_words * (size_t)n_channels;  // uint16 elements
+    const size_t pairs = (total + 1) >> 1;
+    uint32_t *out32 = reinterpret_cast<uint32_t *>(out);
+    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < pairs; q += (size_t)gridDim.x * blockDim.x) {
+        const size_t e0 = 2 * q;
+        const size_t m0 = e0 / n_channels;
+        const int c0 = (int)(e0 - m0 * n_channels);
+        uint32_t v = (words[m0] >> ch[c0]) & 1u;
+        if (e0 + 1 < total) {
+            const int c1 = (c0 + 1 == n_channels) ? 0 : c0 + 1;
+            const size_t m1 = (c0 + 1 == n_channels) ? m0 + 1 : m0;
+            v |= ((words[m1] >> ch[c1]) & 1u) << 16;
+            out32[q] = v;
+        } else {
+            out[e0] = (uint16_t)v;
+        }
+    }
+}
+
+}  // namespace slb

@@ -18,6 +18,28 @@ from . import _lib
 from .safelife_game import ACTION_NAMES, LevelPool, SafeLifeGame
 
 
+class _Info(dict):
+    """The step's info dict (safelife_env.py:176-186).  'board' and 'goals' are uint16 [N,H,W]
+    tensors exported from the resident state when first asked for, not on every step."""
+
+    def __init__(self, game, items):
+        super().__init__(items)
+        self._game = game
+
+    def __missing__(self, key):
+        if key in ("board", "goals"):
+            val = getattr(self._game, key)
+            self[key] = val
+            return val
+        raise KeyError(key)
+
+    def keys(self):
+        return list(super().keys() | {"board", "goals"})
+
+    def __contains__(self, key):
+        return key in ("board", "goals") or super().__contains__(key)
+
+
 class SafeLifeEnv(object):
     metadata = {"render.modes": []}
     action_names = ACTION_NAMES
@@ -96,14 +118,25 @@ class SafeLifeEnv(object):
         vh, vw = self.view_shape
         words = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=self.pool.device)
         with torch.cuda.device(self.pool.device):
-            _lib.check(self._lib.slb_get_obs(self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(),
+            _lib.check(self._lib.slb_get_obs(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
                                              g.state.data_ptr(), vh, vw, int(self.remove_white_goals),
                                              words.data_ptr(), _lib.current_stream()))
-        if not self.output_channels:
-            return words
-        shift = torch.tensor(list(self.output_channels), dtype=torch.int32, device=self.pool.device)
-        bits = (words.to(torch.int32)[..., None] >> shift) & 1
-        return bits.to(torch.uint16)
+            if not self.output_channels:
+                return words
+            ch = self._channels()
+            out = torch.empty((g.n, vh, vw, ch.numel()), dtype=torch.uint16, device=self.pool.device)
+            _lib.check(self._lib.slb_obs_channels(words.data_ptr(), words.numel(), ch.data_ptr(),
+                                                  ch.numel(), out.data_ptr(), _lib.current_stream()))
+        return out
+
+    def _channels(self):
+        key = tuple(self.output_channels)
+        if getattr(self, "_ch_key", None) != key:
+            if len(key) > 16 or any(c < 0 or c > 15 for c in key):
+                raise ValueError("output_channels must be at most 16 bit indices in 0..15")
+            self._ch = torch.tensor(list(key), dtype=torch.uint8, device=self.pool.device)
+            self._ch_key = key
+        return self._ch
 
     def step(self, action):
         """action: int array/tensor [N] (0..8).  Returns (obs, reward int32 [N], done bool [N], info)."""
@@ -113,7 +146,7 @@ class SafeLifeEnv(object):
         already = g._field("episode_completed").clone() if self.global_counter is not None else None
         with torch.cuda.device(self.pool.device):
             _lib.check(self._lib.slb_env_step(
-                self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
                 acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
                 self._done.data_ptr(), self._stride() if self.auto_reset else 0,
                 _lib.current_stream()))
@@ -122,11 +155,11 @@ class SafeLifeEnv(object):
             fresh = already == 0
             self.global_counter.episodes_completed += int((done & fresh).sum().item())
             self.global_counter.num_steps += int(fresh.sum().item())
-        info = {
-            "board": g.board, "goals": g.goals, "agent_loc": g.agent_loc,
+        info = _Info(g, {
+            "agent_loc": g.agent_loc,
             "times_up": g._field("episode_length") > self.time_limit,
             "episode": {"length": g._field("episode_length"), "reward": g._field("episode_reward")},
-        }
+        })
         return (self.get_obs() if self.compute_obs else None), self._reward, done, info
 
     def step_host(self, actions_host, reward_host, done_host):
@@ -135,7 +168,7 @@ class SafeLifeEnv(object):
         g = self.game
         with torch.cuda.device(self.pool.device):
             _lib.check(self._lib.slb_env_step_host(
-                self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
                 _lib.ptr(actions_host), int(self.time_limit), g.seed, g.env_id0,
                 _lib.ptr(reward_host), _lib.ptr(done_host),
                 self._stride() if self.auto_reset else 0, _lib.current_stream()))
@@ -152,7 +185,7 @@ class SafeLifeEnv(object):
             done = torch.empty((T, g.n), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             _lib.check(self._lib.slb_env_rollout(
-                self.pool.c, g.n, g.board.data_ptr(), g.goals.data_ptr(), g.state.data_ptr(),
+                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
                 actions.data_ptr(), int(T), int(self.time_limit), g.seed, g.env_id0,
                 reward.data_ptr(), done.data_ptr(), self._stride() if self.auto_reset else 0,
                 _lib.current_stream()))

@@ -110,11 +110,17 @@ class LevelPool(object):
         self.min_performance = t(rec["min_performance"].astype(np.float64))
         self.baseline = torch.zeros(P, dtype=torch.int32, device=self.device)
         self.exit_mask = torch.zeros((P, H, self.words_per_row), dtype=torch.int32, device=self.device)
+        # levels in the resident (compute) layout + the OR of all cell bits seen (see the header)
+        self.resident_bytes = int(_lib.load().slb_resident_bytes(H, W))
+        self.board_res = torch.zeros(P * self.resident_bytes, dtype=torch.uint8, device=self.device)
+        self.goals_res = torch.zeros_like(self.board_res)
+        self.plane_bits = torch.zeros(2, dtype=torch.int32, device=self.device)
         self.c = _lib.Pool(P, H, W, self.words_per_row, self.board.data_ptr(), self.goals.data_ptr(),
                            self.agent_x.data_ptr(), self.agent_y.data_ptr(),
                            self.orientation.data_ptr(), self.spawn_prob.data_ptr(),
                            self.min_performance.data_ptr(), self.baseline.data_ptr(),
-                           self.exit_mask.data_ptr())
+                           self.exit_mask.data_ptr(), self.board_res.data_ptr(),
+                           self.goals_res.data_ptr(), self.plane_bits.data_ptr())
         with torch.cuda.device(self.device):
             _lib.check(_lib.load().slb_pool_prepare(self.c, _lib.current_stream()))
 
@@ -161,7 +167,9 @@ class SafeLifeGame(object):
     """N lockstep SafeLife games on the device.  Attribute and method names follow the reference's
     SafeLifeGame; values are tensors with a leading env dimension.
 
-    board, goals : uint16 [N,H,W] cuda tensors
+    board, goals : uint16 [N,H,W] cuda tensors — materialised on access from the RESIDENT state
+                   (board_res / goals_res, the bit-sliced layout the kernels compute in; see
+                   include/safelife_b200.h); assigning to them imports the cells
     state        : int32 [N,16] cuda tensor (slb_env_state records)
     """
 
@@ -172,8 +180,8 @@ class SafeLifeGame(object):
         self.n = int(num_envs)
         self.seed, self.env_id0 = int(seed), int(env_id0)
         dev = pool.device
-        self.board = torch.zeros((self.n, pool.h, pool.w), dtype=torch.uint16, device=dev)
-        self.goals = torch.zeros_like(self.board)
+        self.board_res = torch.zeros(self.n * pool.resident_bytes, dtype=torch.uint8, device=dev)
+        self.goals_res = torch.zeros_like(self.board_res)
         self.state = torch.zeros((self.n, 16), dtype=torch.int32, device=dev)
         self._lib = _lib.load()
         if level_ids is None:
@@ -191,6 +199,41 @@ class SafeLifeGame(object):
 
     def state_numpy(self):
         return self.state.cpu().numpy().view(ENV_STATE_DTYPE).reshape(self.n)
+
+    def _export(self, res):
+        out = torch.empty((self.n, self.pool.h, self.pool.w), dtype=torch.uint16, device=self.pool.device)
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_resident_export(res.data_ptr(), out.data_ptr(), self.n,
+                                                     self.pool.h, self.pool.w, self._s()))
+        return out
+
+    def _import(self, cells, res, which):
+        c = torch.as_tensor(cells)
+        if c.dtype == torch.int16:
+            c = c.view(torch.uint16)
+        c = c.to(self.pool.device).contiguous()
+        if c.dtype != torch.uint16 or tuple(c.shape) != (self.n, self.pool.h, self.pool.w):
+            raise ValueError("need a uint16 [N,H,W] array")
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_resident_import(c.data_ptr(), res.data_ptr(), self.n, self.pool.h,
+                                                     self.pool.w, self.pool.plane_bits.data_ptr() + 4 * which,
+                                                     self._s()))
+
+    @property
+    def board(self):
+        return self._export(self.board_res)
+
+    @board.setter
+    def board(self, cells):
+        self._import(cells, self.board_res, 0)
+
+    @property
+    def goals(self):
+        return self._export(self.goals_res)
+
+    @goals.setter
+    def goals(self, cells):
+        self._import(cells, self.goals_res, 1)
 
     # -- reference attributes ---------------------------------------------------------------
     @property
@@ -249,7 +292,7 @@ class SafeLifeGame(object):
             m = torch.as_tensor(mask).to(self.pool.device).to(torch.uint8).contiguous()
         with torch.cuda.device(self.pool.device):
             _lib.check(self._lib.slb_env_reset(self.pool.c, self.n, lv.data_ptr(), _lib.ptr(m),
-                                               self.board.data_ptr(), self.goals.data_ptr(),
+                                               self.board_res.data_ptr(), self.goals_res.data_ptr(),
                                                self.state.data_ptr(), self._s()))
         return True
 
@@ -259,9 +302,9 @@ class SafeLifeGame(object):
         acts = self._actions(action)
         reward = torch.empty(self.n, dtype=torch.int32, device=self.pool.device)
         with torch.cuda.device(self.pool.device):
-            _lib.check(self._lib.slb_execute_action(self.board.data_ptr(), self.n, self.pool.h,
-                                                    self.pool.w, self.state.data_ptr(),
-                                                    acts.data_ptr(), reward.data_ptr(), self._s()))
+            _lib.check(self._lib.slb_execute_action(self.pool.c, self.n, self.board_res.data_ptr(),
+                                                    self.state.data_ptr(), acts.data_ptr(),
+                                                    reward.data_ptr(), self._s()))
         return reward
 
     def _actions(self, action):
@@ -279,18 +322,10 @@ class SafeLifeGame(object):
     def advance_board(self):
         """SafeLifeGame.advance_board (safelife_game.py:657-660): num_steps += 1, board then goals
         (that is the order the per-env stream is consumed in)."""
-        p = self.spawn_prob.contiguous()
-        ctr = self._field("rng_counter").contiguous()
-        nb, ng = torch.empty_like(self.board), torch.empty_like(self.goals)
         with torch.cuda.device(self.pool.device):
-            for src, dst in ((self.board, nb), (self.goals, ng)):
-                _lib.check(self._lib.slb_advance_board(src.data_ptr(), dst.data_ptr(), self.n,
-                                                       self.pool.h, self.pool.w, p.data_ptr(),
-                                                       self.seed, self.env_id0, ctr.data_ptr(), 1,
-                                                       None, self._s()))
-        self.board, self.goals = nb, ng
-        self._field("rng_counter").copy_(ctr)
-        self._field("num_steps").add_(1)
+            _lib.check(self._lib.slb_game_advance(self.pool.c, self.n, self.board_res.data_ptr(),
+                                                  self.goals_res.data_ptr(), self.state.data_ptr(),
+                                                  self.seed, self.env_id0, self._s()))
 
     def _points_perf(self):
         dev = self.pool.device
@@ -298,7 +333,7 @@ class SafeLifeGame(object):
         ce = torch.empty(self.n, dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             _lib.check(self._lib.slb_points_and_performance(
-                self.pool.c, self.n, self.board.data_ptr(), self.goals.data_ptr(),
+                self.pool.c, self.n, self.board_res.data_ptr(), self.goals_res.data_ptr(),
                 self.state.data_ptr(), out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
                 ce.data_ptr(), self._s()))
         return out[0], out[1], out[2], ce
@@ -316,8 +351,8 @@ class SafeLifeGame(object):
 
     def update_exit_colors(self):
         with torch.cuda.device(self.pool.device):
-            _lib.check(self._lib.slb_update_exit_colors(self.pool.c, self.n, self.board.data_ptr(),
-                                                        self.goals.data_ptr(), self.state.data_ptr(),
+            _lib.check(self._lib.slb_update_exit_colors(self.pool.c, self.n, self.board_res.data_ptr(),
+                                                        self.goals_res.data_ptr(), self.state.data_ptr(),
                                                         self._s()))
 
     @property
