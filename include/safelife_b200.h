@@ -79,8 +79,10 @@ typedef struct {
     uint32_t *exit_mask;            /* [P,H,words_per_row] written by slb_pool_prepare */
     void *board_res;                /* [P] boards in the RESIDENT format, written by slb_pool_prepare */
     void *goals_res;                /* [P] goals  in the RESIDENT format, written by slb_pool_prepare */
-    uint32_t *plane_bits;           /* [2] OR of every board / goals cell seen (pool + imports); zeroed
-                                       by the caller, maintained by slb_pool_prepare / slb_resident_import */
+    uint32_t *plane_bits;           /* [2] device: OR of every board / goals cell seen (pool + imports);
+                                       zeroed by the caller, maintained by slb_pool_prepare / _import */
+    uint32_t plane_groups[2];       /* host copy as plane-group masks (bit g = group g in use) for boards /
+                                       goals; written by slb_pool_prepare and slb_resident_import */
 } slb_pool;
 
 /* ---- RESIDENT env state ------------------------------------------------------------------------
@@ -97,15 +99,17 @@ typedef struct {
  * format of every other boundary: level pool, speedups.advance_board, side effects, observations).
  */
 size_t slb_resident_bytes(int h, int w);
-/* d_cells [N,H,W] uint16 -> d_res.  pool_plane_bits: &pool->plane_bits[0] for boards, [1] for
- * goals (device pointer; may be NULL for a conversion that no env kernel will read). */
+/* d_cells [N,H,W] uint16 -> d_res.  `pool` (may be NULL for a conversion that no env kernel will
+ * read) is the pool whose envs the boards join, which = 0 for boards, 1 for goals: the cells' bits
+ * are ORed into pool->plane_bits[which] and, after a stream synchronisation, pool->plane_groups. */
 int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int w,
-                        uint32_t *pool_plane_bits, void *stream);
+                        slb_pool *pool, int which, void *stream);
 int slb_resident_export(const void *d_res, uint16_t *d_cells, int n, int h, int w, void *stream);
 
 /* Fills pool->baseline (performance_ratio's baseline_score, safelife_game.py:622),
- * pool->exit_mask (update_exit_locs, :528-529), the resident copies of the levels and plane_bits. */
-int slb_pool_prepare(const slb_pool *pool, void *stream);
+ * pool->exit_mask (update_exit_locs, :528-529), the resident copies of the levels, plane_bits and
+ * (synchronising the stream once) plane_groups. */
+int slb_pool_prepare(slb_pool *pool, void *stream);
 
 /* ---- A1-A4: speedups.advance_board for N boards (module.c:19-44 -> advance_board.c:34-120) ----
  * d_in/d_out: [N,H,W] uint16, d_in != d_out.  d_spawn_prob: [N] float.  Env ids are env_id0 + i.

@@ -32,6 +32,7 @@ class Pool(C.Structure):
         ("spawn_prob", C.c_void_p), ("min_performance", C.c_void_p),
         ("baseline", C.c_void_p), ("exit_mask", C.c_void_p),
         ("board_res", C.c_void_p), ("goals_res", C.c_void_p), ("plane_bits", C.c_void_p),
+        ("plane_groups", C.c_uint32 * 2),
     ]
 
 
@@ -44,7 +45,7 @@ SYMBOLS = {
     "slb_launch_count": (_u64, []),
     "slb_pool_prepare": (_i, [_PP, _vp]),
     "slb_resident_bytes": (_sz, [_i, _i]),
-    "slb_resident_import": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "slb_resident_import": (_i, [_vp, _vp, _i, _i, _i, _PP, _i, _vp]),
     "slb_resident_export": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "slb_advance_board": (_i, [_vp, _vp, _i, _i, _i, _vp, _u64, _u64, _vp, _i, _vp, _vp]),
     "slb_advance_board_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _u64, _u64, _vp, _i]),

@@ -93,10 +93,22 @@ size_t slb_resident_bytes(int h, int w) {
     return fast_shape(h, w) ? resident_words(h) * 4 : (size_t)h * w * 2;
 }
 
+static int refresh_groups(slb_pool *pool, cudaStream_t st) {
+    uint32_t bits[2] = {0, 0};
+    SLB_CUDA(cudaMemcpyAsync(bits, pool->plane_bits, sizeof(bits), cudaMemcpyDeviceToHost, st));
+    SLB_CUDA(cudaStreamSynchronize(st));
+    pool->plane_groups[0] = groups_of(bits[0]);
+    pool->plane_groups[1] = groups_of(bits[1]);
+    return SLB_OK;
+}
+
 int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int w,
-                        uint32_t *pool_plane_bits, void *stream) {
+                        slb_pool *pool, int which, void *stream) {
     if (int rc = check_shape(n, h, w)) return rc;
     if (!d_cells || !d_res) return fail(SLB_ERR_INVALID, "slb_resident_import: NULL pointer");
+    if (pool && (which < 0 || which > 1 || !pool->plane_bits || pool->h != h || pool->w != w))
+        return fail(SLB_ERR_INVALID, "slb_resident_import: pool / which do not match the boards");
+    uint32_t *pool_plane_bits = pool ? pool->plane_bits + which : nullptr;
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (!fast_shape(h, w)) {
@@ -107,6 +119,7 @@ int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int 
     res_import_kernel<<<(n + RES_WARPS - 1) / RES_WARPS, RES_WARPS * 32, 0, st>>>(
         d_cells, (uint32_t *)d_res, n, h, w, pool_plane_bits, fast_vec_ok(h, w, d_cells, d_cells));
     SLB_LAUNCHED();
+    if (pool) return refresh_groups(pool, st);
     return SLB_OK;
 }
 
@@ -126,15 +139,15 @@ int slb_resident_export(const void *d_res, uint16_t *d_cells, int n, int h, int 
     return SLB_OK;
 }
 
-int slb_pool_prepare(const slb_pool *pool, void *stream) {
+int slb_pool_prepare(slb_pool *pool, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     pool_prepare_kernel<<<pool->n_levels, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool);
     SLB_LAUNCHED();
     if (fast_shape(pool->h, pool->w)) {
         if (int rc = slb_resident_import(pool->board, pool->board_res, pool->n_levels, pool->h, pool->w,
-                                         pool->plane_bits, stream)) return rc;
+                                         pool, 0, stream)) return rc;
         if (int rc = slb_resident_import(pool->goals, pool->goals_res, pool->n_levels, pool->h, pool->w,
-                                         pool->plane_bits + 1, stream)) return rc;
+                                         pool, 1, stream)) return rc;
     }
     return SLB_OK;
 }
@@ -321,9 +334,8 @@ int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (fast_shape(pool->h, pool->w)) {
-        res_env_rollout_kernel<<<RES_GRID(n), st>>>(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals,
-                                                   d_state, d_actions, 1, time_limit, seed, env_id0,
-                                                   d_reward, d_done, auto_reset_stride);
+        launch_res_env_rollout(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions, 1,
+                               time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, st);
         SLB_LAUNCHED();
         return SLB_OK;
     }
@@ -348,9 +360,9 @@ int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
         return fail(SLB_ERR_INVALID, "slb_env_rollout: bad arguments");
     if (n == 0 || t_steps == 0) return SLB_OK;
     if (fast_shape(pool->h, pool->w)) {
-        res_env_rollout_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(
-            *pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions, t_steps, time_limit,
-            seed, env_id0, d_reward, d_done, auto_reset_stride);
+        launch_res_env_rollout(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions,
+                               t_steps, time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride,
+                               (cudaStream_t)stream);
         SLB_LAUNCHED();
         return SLB_OK;
     }

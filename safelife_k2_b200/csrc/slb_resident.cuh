@@ -144,6 +144,9 @@ __device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, c
 // A12 fused: T env steps per launch (T = 1 with a policy in the loop); board + goals stay in
 // registers between steps.  grid = ceil(N / RES_WARPS).
 // ---------------------------------------------------------------------------------------------
+// GB / GG: compile-time plane-group masks of boards / goals (supersets of pool.plane_groups):
+// planes of absent groups are constant zero, so their registers and all work on them fold away.
+template <unsigned GB, unsigned GG>
 __global__ void __launch_bounds__(RES_WARPS * 32, 7)
 res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                        const uint8_t *__restrict__ actions, int t_steps, int time_limit,
@@ -154,13 +157,12 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
     if (i >= n) return;
     const Geo g = make_geo(pool.h, pool.w);
     const size_t words = resident_words(g.h);
-    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
     uint32_t *bp = board + i * words, *gp = goals + i * words;
     uint32_t B[16], G[16];
-    load_res(bp, g, gb, B);
-    load_res(gp, g, gg, G);
     EnvRegs e = load_env(state + i);
     int action = actions[i];
+    load_res(bp, g, GB, B);
+    load_res(gp, g, GG, G);
     LevelConsts lc = load_level(pool, e.level, g);
     const uint64_t env = env_id0 + (uint64_t)i;
     bool g_dirty = false;
@@ -186,14 +188,30 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
             if (done_out) done_out[(size_t)t * n + i] = (uint8_t)done;
         }
         if (done && auto_reset_stride > 0) {
-            reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, gb, gg, B, G, lc, e);
+            reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
             g_dirty = true;
         }
         action = next_action;
     }
-    store_res(bp, g, gb, B);
-    if (g_dirty) store_res(gp, g, gg, G);
+    store_res(bp, g, GB, B);
+    if (g_dirty) store_res(gp, g, GG, G);
     if (lane == 0) store_env(state + i, e);
+}
+
+// picks the smallest instantiated superset of the pool's plane groups
+inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board, uint32_t *goals,
+                                   slb_env_state *state, const uint8_t *actions, int t_steps,
+                                   int time_limit, uint64_t seed, uint64_t env0, int32_t *reward,
+                                   uint8_t *done, int stride, cudaStream_t st) {
+    const int grid = (n + RES_WARPS - 1) / RES_WARPS;
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
+#define SLB_ROLL(GBV, GGV)                                                                           \
+    res_env_rollout_kernel<GBV, GGV><<<grid, RES_WARPS * 32, 0, st>>>(                                \
+        pool, n, board, goals, state, actions, t_steps, time_limit, seed, env0, reward, done, stride)
+    if (!(gg & ~3u) && !(gb & ~7u)) SLB_ROLL(7u, 3u);        // no spawners anywhere, plain goals
+    else if (!(gg & ~3u)) SLB_ROLL(15u, 3u);                 // spawners on the boards, plain goals
+    else SLB_ROLL(15u, 15u);
+#undef SLB_ROLL
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -208,7 +226,7 @@ res_reset_kernel(slb_pool pool, int n, const int32_t *__restrict__ level_ids,
     if (i >= n || (mask && !mask[i])) return;
     const Geo g = make_geo(pool.h, pool.w);
     const size_t words = resident_words(g.h);
-    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     uint32_t B[16], G[16];
     LevelConsts lc;
     EnvRegs e = load_env(state + i);
@@ -226,7 +244,7 @@ res_action_kernel(slb_pool pool, int n, uint32_t *board, slb_env_state *state,
     const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
     if (i >= n) return;
     const Geo g = make_geo(pool.h, pool.w);
-    const unsigned gb = groups_of(pool.plane_bits[0]);
+    const unsigned gb = pool.plane_groups[0];
     uint32_t *bp = board + i * resident_words(g.h);
     uint32_t B[16];
     load_res(bp, g, gb, B);
@@ -249,7 +267,7 @@ res_advance_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_e
     if (i >= n) return;
     const Geo g = make_geo(pool.h, pool.w);
     const size_t words = resident_words(g.h);
-    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     uint32_t P[16];
     EnvRegs e = load_env(state + i);
     const float p = pool.spawn_prob[e.level];
@@ -275,7 +293,7 @@ res_score_kernel(slb_pool pool, int n, uint32_t *board, const uint32_t *goals, s
     if (i >= n) return;
     const Geo g = make_geo(pool.h, pool.w);
     const size_t words = resident_words(g.h);
-    const unsigned gb = groups_of(pool.plane_bits[0]), gg = groups_of(pool.plane_bits[1]);
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     uint32_t B[16], G[16];
     load_res(board + i * words, g, gb, B);
     load_res(goals + i * words, g, gg, G);
@@ -355,7 +373,7 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
     const int h = g.h, w = g.w, S = row_stride(w);
     const size_t words = resident_words(h);
     uint32_t O[16], G[16];
-    load_res(board + i * words, g, groups_of(pool.plane_bits[0]), O);
+    load_res(board + i * words, g, pool.plane_groups[0], O);
     load_res(goals + i * words, g, 3u, G);  // only the colour planes (groups 0/1) are needed
     {
         uint32_t cr = G[9], cg = G[10], cb = G[11];

@@ -10,6 +10,8 @@ GameWithGoals :540-647 (point_table :554-565, current_points :590-599, performan
 
 Out of scope here: level editing (execute_edit), GameOfLife / AsyncGame.
 """
+import ctypes as C
+
 import numpy as np
 import torch
 
@@ -120,7 +122,8 @@ class LevelPool(object):
                            self.orientation.data_ptr(), self.spawn_prob.data_ptr(),
                            self.min_performance.data_ptr(), self.baseline.data_ptr(),
                            self.exit_mask.data_ptr(), self.board_res.data_ptr(),
-                           self.goals_res.data_ptr(), self.plane_bits.data_ptr())
+                           self.goals_res.data_ptr(), self.plane_bits.data_ptr(),
+                           (C.c_uint32 * 2)(0, 0))
         with torch.cuda.device(self.device):
             _lib.check(_lib.load().slb_pool_prepare(self.c, _lib.current_stream()))
 
@@ -216,8 +219,7 @@ class SafeLifeGame(object):
             raise ValueError("need a uint16 [N,H,W] array")
         with torch.cuda.device(self.pool.device):
             _lib.check(self._lib.slb_resident_import(c.data_ptr(), res.data_ptr(), self.n, self.pool.h,
-                                                     self.pool.w, self.pool.plane_bits.data_ptr() + 4 * which,
-                                                     self._s()))
+                                                     self.pool.w, self.pool.c, which, self._s()))
 
     @property
     def board(self):
