@@ -138,11 +138,11 @@ def run_b200(args):
     rank, world, local = distributed.init_from_env()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    n = ENVS_PER_GPU
+    n = args.envs
     lo = rank * n
     lv = append_still_levels()
     pool = LevelPool(lv, device=dev)
-    state_bytes = n * (2 * H * W * 2 + 64)
+    state_bytes = n * (2 * 64 * H + 64)  # resident: 64*H B per board, 64 B scalars
     ring = max(4, int(np.ceil(2.2 * L2_BYTES / state_bytes)))
     K, Wm = args.steps, max(3, args.warmup)
 
@@ -238,7 +238,7 @@ def run_b200(args):
         "metric": "env_steps_per_s", "value": value, "unit": "env-steps/s", "n_gpus": world,
         "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u16", "data": "synthetic",
-        "config": {"workload": "append-still 26x26, 4096 lockstep envs per GPU, random actions, full env step "
+        "config": {"workload": "append-still 26x26, %d lockstep envs per GPU, random actions, full env step " % n +
                                "(execute_action + advance_board x2 + reward + exit colours), k=1 step per launch",
                    "envs_per_gpu": n, "board": [H, W], "l2": "ring of %d independent batches (%.0f MB state) > L2" % (
                        ring, ring * state_bytes / 1e6)},
@@ -247,7 +247,7 @@ def run_b200(args):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "bytes_per_env_step": BYTES_PER_ENV_STEP, "kernel": "env step (per launch: 4096 envs)"},
+                     "bytes_per_env_step": BYTES_PER_ENV_STEP, "kernel": "res_env_rollout_kernel, T=1 (per launch: %d envs)" % n},
         "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": n,
                 "d2h_bytes_per_step": 5 * n, "steps": e2e_steps,
                 "what": "slb_env_step_host: pinned uint8 actions H2D, fused step, int32 reward + uint8 done D2H, sync"},
@@ -269,6 +269,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="envs per GPU per step (default: the BASELINE config)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python (host-bound)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -17,6 +17,8 @@
 // The uint16 [N,H,W] cell layout of the reference stays the format of every API boundary
 // (slb_resident_import / slb_resident_export, slb_advance_board, the level pool, observations).
 #pragma once
+#include <cstdlib>
+
 #include "slb_planes_env.cuh"
 
 namespace slb {
@@ -154,11 +156,15 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
                        int auto_reset_stride) {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    // Programmatic dependent launch: let the next kernel on the stream begin launching now (its CTAs
+    // take the SM slots ours free up); wait for the previous kernel's writes before the first read.
+    asm volatile("griddepcontrol.launch_dependents;");
     if (i >= n) return;
     const Geo g = make_geo(pool.h, pool.w);
     const size_t words = resident_words(g.h);
     uint32_t *bp = board + i * words, *gp = goals + i * words;
     uint32_t B[16], G[16];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
     int action = actions[i];
     load_res(bp, g, GB, B);
@@ -205,9 +211,21 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
                                    uint8_t *done, int stride, cudaStream_t st) {
     const int grid = (n + RES_WARPS - 1) / RES_WARPS;
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
+    // launched with programmatic stream serialization (see the griddepcontrol pair in the kernel)
+    static const bool pdl = []() { const char *v = getenv("SLB_PDL"); return !v || v[0] != '0'; }();
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(RES_WARPS * 32);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
 #define SLB_ROLL(GBV, GGV)                                                                           \
-    res_env_rollout_kernel<GBV, GGV><<<grid, RES_WARPS * 32, 0, st>>>(                                \
-        pool, n, board, goals, state, actions, t_steps, time_limit, seed, env0, reward, done, stride)
+    cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV>, pool, n, board, goals, state, actions, \
+                       t_steps, time_limit, seed, env0, reward, done, stride)
     if (!(gg & ~3u) && !(gb & ~7u)) SLB_ROLL(7u, 3u);        // no spawners anywhere, plain goals
     else if (!(gg & ~3u)) SLB_ROLL(15u, 3u);                 // spawners on the boards, plain goals
     else SLB_ROLL(15u, 15u);
