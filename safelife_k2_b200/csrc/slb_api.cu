@@ -334,6 +334,8 @@ int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (fast_shape(pool->h, pool->w)) {
+        if ((uint64_t)n * 16u * (uint64_t)pool->h >= (1ull << 32))
+            return fail(SLB_ERR_UNSUPPORTED, "too many envs per launch (resident word offsets are 32-bit)");
         launch_res_env_rollout(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions, 1,
                                time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, st);
         SLB_LAUNCHED();
@@ -360,6 +362,8 @@ int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
         return fail(SLB_ERR_INVALID, "slb_env_rollout: bad arguments");
     if (n == 0 || t_steps == 0) return SLB_OK;
     if (fast_shape(pool->h, pool->w)) {
+        if ((uint64_t)n * 16u * (uint64_t)pool->h >= (1ull << 32))
+            return fail(SLB_ERR_UNSUPPORTED, "too many envs per launch (resident word offsets are 32-bit)");
         launch_res_env_rollout(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions,
                                t_steps, time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride,
                                (cudaStream_t)stream);

@@ -23,7 +23,8 @@ __device__ __forceinline__ int action_planes(uint32_t P[16], const Geo &g, int &
     const int lane = threadIdx.x & 31;
     const int dir = (action - 1) & 3;
     orientation = dir;
-    const int fx = (dir == 1) - (dir == 3), fy = (dir == 2) - (dir == 0);
+    // forward vector: up (0,-1), right (1,0), down (0,1), left (-1,0)
+    const int fx = (dir & 1) ? 2 - dir : 0, fy = (dir & 1) ? 0 : dir - 1;
     const int h = g.h, w = g.w;
     int xF = ax + fx, yF = ay + fy;
     xF = xF < 0 ? w - 1 : (xF >= w ? 0 : xF);

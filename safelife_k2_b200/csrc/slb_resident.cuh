@@ -148,7 +148,8 @@ __device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, c
 // ---------------------------------------------------------------------------------------------
 // GB / GG: compile-time plane-group masks of boards / goals (supersets of pool.plane_groups):
 // planes of absent groups are constant zero, so their registers and all work on them fold away.
-template <unsigned GB, unsigned GG>
+// HW: board height = width when known at compile time (26: the benchmark levels), 0 = run time.
+template <unsigned GB, unsigned GG, int HW>
 __global__ void __launch_bounds__(RES_WARPS * 32, 7)
 res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                        const uint8_t *__restrict__ actions, int t_steps, int time_limit,
@@ -160,9 +161,9 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
     // take the SM slots ours free up); wait for the previous kernel's writes before the first read.
     asm volatile("griddepcontrol.launch_dependents;");
     if (i >= n) return;
-    const Geo g = make_geo(pool.h, pool.w);
-    const size_t words = resident_words(g.h);
-    uint32_t *bp = board + i * words, *gp = goals + i * words;
+    const Geo g = make_geo(HW ? HW : pool.h, HW ? HW : pool.w);
+    const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);  // resident words per board: 16 * H
+    uint32_t *bp = board + off, *gp = goals + off;
     uint32_t B[16], G[16];
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
@@ -223,12 +224,18 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
     cfg.stream = st;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
+#define SLB_ROLL2(GBV, GGV, HWV)                                                                     \
+    cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV, HWV>, pool, n, board, goals, state,     \
+                       actions, t_steps, time_limit, seed, env0, reward, done, stride)
 #define SLB_ROLL(GBV, GGV)                                                                           \
-    cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV>, pool, n, board, goals, state, actions, \
-                       t_steps, time_limit, seed, env0, reward, done, stride)
+    do {                                                                                             \
+        if (pool.h == 26 && pool.w == 26) SLB_ROLL2(GBV, GGV, 26);                                   \
+        else SLB_ROLL2(GBV, GGV, 0);                                                                 \
+    } while (0)
     if (!(gg & ~3u) && !(gb & ~7u)) SLB_ROLL(7u, 3u);        // no spawners anywhere, plain goals
     else if (!(gg & ~3u)) SLB_ROLL(15u, 3u);                 // spawners on the boards, plain goals
     else SLB_ROLL(15u, 15u);
+#undef SLB_ROLL2
 #undef SLB_ROLL
 }
 
