@@ -299,3 +299,36 @@ class OracleBatchEnv(object):
             for f in futs:
                 f.result()
         return rewards, dones
+
+
+# ---------------------------------------------------------------------------------------------
+# observation (numpy restatement; pinned by tests/golden/obs.npz)
+# ---------------------------------------------------------------------------------------------
+def get_obs(board, goals, agent_loc, board0, view_shape=(15, 15), remove_white_goals=True,
+            output_channels=tuple(range(15))):
+    """SafeLifeEnv.get_obs (safelife_env.py:125-155) + recenter_view (helper_utils.py:41-74) for one
+    env.  agent_loc = (x, y); board0 = the level's initial board (its exit cells are exit_locs,
+    safelife_game.py:528-529)."""
+    board = np.array(board, dtype=np.uint16)
+    g = np.asarray(goals, dtype=np.uint16) & np.uint16(7 << 9)             # :134
+    if remove_white_goals:
+        g = g * (g != np.uint16(7 << 9)).astype(np.uint16)                 # :139-140
+    board = (board + (g << np.uint16(3))).astype(np.uint16)                # :143, uint16 wrap
+    h, w = view_shape
+    bh, bw = board.shape
+    x0, y0 = int(agent_loc[0]), int(agent_loc[1])
+    x1, y1 = x0 - w // 2, y0 - h // 2                                      # helper_utils.py:58-59
+    ys = (y1 + np.arange(h)) % bh
+    xs = (x1 + np.arange(w)) % bw
+    view = board[np.ix_(ys, xs)].copy()                                    # wrapping_array slice :60
+    iy, ix = np.nonzero(np.asarray(board0, dtype=np.uint16) & np.uint16(256))  # exit_locs
+    jy = (iy - y0 + bh // 2) % bh - bh // 2                                # :66-67
+    jx = (ix - x0 + bw // 2) % bw - bw // 2
+    jy = np.clip(jy + h // 2, 0, h - 1)                                    # :69-70
+    jx = np.clip(jx + w // 2, 0, w - 1)
+    for k in range(len(iy)):                                               # :72, last write wins
+        view[jy[k], jx[k]] = board[iy[k], ix[k]]
+    if output_channels:                                                    # :152-154
+        shift = np.array(list(output_channels), dtype=np.uint16)
+        view = (view[..., None] & (np.uint16(1) << shift)) >> shift
+    return view

@@ -13,6 +13,7 @@ Outputs (all np.savez_compressed):
     trace_*.npz       full per-step SafeLifeEnv traces (config 1 append-still; prune-spawn stochastic)
     scenarios.npz     scripted execute_action cases on real SafeLifeGame objects (push/pull/exit/toggle)
     side_effects.npz  pre-EMD density counts of side_effect_score for finished episodes
+    obs.npz           SafeLifeEnv.get_obs along short traces (several view shapes / channel sets)
 """
 import hashlib
 import os
@@ -295,9 +296,47 @@ def make_side_effects():
     save("side_effects.npz", **out)
 
 
+# -------------------------------------------------------------------------------------------------
+def make_obs():
+    """SafeLifeEnv.get_obs (safelife_env.py:125-155) of the real reference env along short traces:
+    default 15x15x15 channels, packed words, a view larger than the board (33x33, the training
+    view), an even-sized view, white goals kept."""
+    cases = [
+        ("append-still", 4, 11, 12, 3, (15, 15), True, tuple(range(15))),
+        ("prune-spawn", 9, 13, 14, 4, (33, 33), True, None),
+        ("navigation", 2, 15, 16, 5, (9, 12), False, (0, 1, 4, 8, 9, 10, 11, 12, 13, 14)),
+        ("append-dynamic", 30, 17, 18, 6, (15, 15), False, None),
+        ("prune-still-hard", 7, 19, 20, 7, (26, 26), True, None),
+    ]
+    out = {"n_cases": np.int32(len(cases))}
+    T, every = 80, 4
+    for i, (archive, level, s, a, env_id, view, rw, ch) in enumerate(cases):
+        lv = rh.load_archive("benchmarks/v1.0/" + archive)
+        rng = np.random.RandomState(a)
+        actions = np.array([int(rng.randint(9)) for _ in range(T)], dtype=np.int32)
+        ctx = rh.fed_reference(s, env_id)
+        with ctx:
+            env = rh.make_env(levels=lv[level:level + 1], global_counter=None, view_shape=view,
+                              remove_white_goals=rw, output_channels=ch)
+            obs = [np.asarray(env.reset()).astype(np.uint16)]
+            ctx.rewind(0)
+            for t, act in enumerate(actions):
+                o, r, done, info = env.step(int(act))
+                if (t + 1) % every == 0:
+                    obs.append(np.asarray(o).astype(np.uint16))
+        out.update({
+            "archive_%d" % i: np.array(archive), "level_%d" % i: np.int32(level), "seed_%d" % i: np.uint64(s),
+            "env_%d" % i: np.uint64(env_id), "actions_%d" % i: actions, "view_%d" % i: np.array(view, np.int32),
+            "remove_white_%d" % i: np.int32(rw), "channels_%d" % i: np.array(ch if ch else [], np.int32),
+            "every_%d" % i: np.int32(every), "obs_%d" % i: np.stack(obs),
+        })
+        print("  obs %s view %s -> %s" % (archive, view, np.stack(obs).shape))
+    save("obs.npz", **out)
+
+
 if __name__ == "__main__":
     assert rh.available(), "needs /root/reference and `make -C oracle ref`"
-    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side"]
+    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs"]
     if "levels" in which:
         make_levels()
     if "kat" in which:
@@ -308,3 +347,5 @@ if __name__ == "__main__":
         make_scenarios()
     if "side" in which:
         make_side_effects()
+    if "obs" in which:
+        make_obs()

@@ -261,3 +261,117 @@ def test_stats_accumulate(sl):
         tot_r += int(r.sum()); tot_d += int(d.sum())
     s = stats.cpu().numpy()
     assert s[0] == tot_r and s[1] == tot_d and s[6] == 1500
+
+
+def test_get_obs_golden(sl):
+    """slb_get_obs + slb_obs_channels against the reference's SafeLifeEnv.get_obs (tests/golden/obs.npz)"""
+    d = gu.load("obs.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        pool = sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 1))
+        view = tuple(int(v) for v in d["view_%d" % i])
+        ch = tuple(int(c) for c in d["channels_%d" % i]) or None
+        env = sl.env.SafeLifeEnv(pool, num_envs=1, env_id0=int(d["env_%d" % i]), global_counter=None,
+                                 view_shape=view, remove_white_goals=bool(d["remove_white_%d" % i]),
+                                 output_channels=ch)
+        env.seed(int(d["seed_%d" % i]))
+        want = d["obs_%d" % i]
+        obs = env.reset()
+        assert obs.dtype == torch.uint16 and (obs[0].cpu().numpy() == want[0]).all(), (i, "reset")
+        k = 1
+        for t, a in enumerate(d["actions_%d" % i]):
+            obs, _, _, _ = env.step(np.array([a]))
+            if (t + 1) % int(d["every_%d" % i]) == 0:
+                assert (obs[0].cpu().numpy() == want[k]).all(), (i, t)
+                k += 1
+
+
+def _random_levels(rng, p, h, w, exits=2):
+    """Dense little levels full of crates / walls / life so that random actions push, pull, wrap,
+    toggle and exit all the time."""
+    vals = np.array([0, 0, 0, 1033, 521, 16, 1041, 32788, 32788, 1688, 9, 20, 32784 | 1], np.uint16)
+    board = vals[rng.randint(len(vals), size=(p, h, w))]
+    goals = np.array([0, 0, 2057, 3584, 1033, 16], np.uint16)[rng.randint(6, size=(p, h, w))]
+    agent = np.stack([rng.randint(w, size=p), rng.randint(h, size=p)], 1)
+    for l in range(p):
+        for _ in range(exits):
+            board[l, rng.randint(h), rng.randint(w)] = 272
+        board[l, agent[l, 1], agent[l, 0]] = 122 | (rng.randint(8) << 9)
+    return {"board": board, "goals": goals, "agent_loc": agent, "orientation": rng.randint(4, size=p),
+            "spawn_prob": rng.choice([0.0, 0.3, 1.0], size=p), "min_performance": rng.choice([-1.0, 0.0, 0.01], size=p)}
+
+
+@pytest.mark.parametrize("h,w", [(4, 4), (5, 7), (26, 26), (32, 32), (31, 9), (9, 31), (3, 5), (40, 33)])
+def test_action_stress_vs_oracle(sl, h, w):
+    """Random actions on dense random levels of odd shapes (toroidal push / pull / exit / toggle at the
+    seams, spawners, auto-reset): full state equality with the oracle every few steps.  Shapes outside
+    4..32 take the uint16-resident generic kernels, the others the resident bit-plane kernels."""
+    rng = np.random.RandomState(h * 100 + w)
+    lv = _random_levels(rng, 24, h, w)
+    n, steps = 96, 60
+    pool = sl.game.LevelPool(lv)
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=5, global_counter=None, auto_reset=True, time_limit=25,
+                             view_shape=(7, 9), output_channels=None)
+    env.seed(h + w)
+    obs = env.reset()
+    lvl = (np.arange(n) + 5) % pool.n_levels
+    oenv = slo.OracleBatchEnv(slo.OraclePool(**lv), lvl, seed=h + w, env_id0=5, threads=4, time_limit=25)
+    stride = n % pool.n_levels or pool.n_levels
+
+    def check(t):
+        assert (env.game.board.cpu().numpy() == oenv.boards).all(), t
+        assert (env.game.goals.cpu().numpy() == oenv.goals).all(), t
+        st, ost = env.game.state_numpy(), oenv.states
+        for f in st.dtype.names:
+            assert (st[f] == ost[f]).all(), (f, t)
+        o = obs.cpu().numpy()
+        for i in range(0, n, 7):
+            want = slo.get_obs(oenv.boards[i], oenv.goals[i], (ost["agent_x"][i], ost["agent_y"][i]),
+                               lv["board"][ost["level_id"][i]], (7, 9), True, None)
+            assert (o[i] == want).all(), (t, i)
+
+    check(-1)
+    for t in range(steps):
+        acts = rng.randint(9, size=n)
+        obs, r, d, _ = env.step(acts)
+        orr, od = oenv.step(acts)
+        assert (r.cpu().numpy() == orr).all(), t
+        assert (d.cpu().numpy() == (od != 0)).all(), t
+        if od.any():
+            idx = np.nonzero(od)[0]
+            lvl[idx] = (lvl[idx] + stride) % pool.n_levels
+            oenv.reset(idx, lvl[idx])
+        if t % 3 == 0 or t == steps - 1:
+            check(t)
+
+
+def test_resident_import_export_roundtrip(sl):
+    """cells -> resident planes -> cells is the identity for every uint16 value (incl. bits 12-14), and a
+    board imported into a game with bits its pool had never seen is stepped correctly afterwards."""
+    rng = np.random.RandomState(3)
+    L = sl.lib.load()
+    for h, w in [(26, 26), (4, 32), (32, 4), (17, 23), (40, 5)]:
+        cells = torch.from_numpy(rng.randint(0, 1 << 16, size=(50, h, w)).astype(np.uint16)).cuda()
+        res = torch.zeros(50 * L.slb_resident_bytes(h, w), dtype=torch.uint8, device="cuda")
+        back = torch.zeros_like(cells)
+        sl.lib.check(L.slb_resident_import(cells.data_ptr(), res.data_ptr(), 50, h, w, None, 0, None))
+        sl.lib.check(L.slb_resident_export(res.data_ptr(), back.data_ptr(), 50, h, w, None))
+        assert (back == cells).all(), (h, w)
+    # a pool without spawners; then a board WITH a spawner is assigned to the game
+    lv = gu.level_slice(gu.levels("append-still"), 0, 4)
+    pool = sl.game.LevelPool(lv)
+    assert pool.c.plane_groups[0] == 7 and pool.c.plane_groups[1] == 3
+    g = sl.game.SafeLifeGame(pool, 4, seed=2)
+    b = g.board.cpu().numpy()
+    b[:, 5, 5] = 1688
+    b[:, 7, 7] = 0x7000 | 16
+    g.board = torch.from_numpy(b).cuda()
+    assert pool.c.plane_groups[0] == 15
+    ctr = np.zeros(4, np.uint64)
+    for t in range(5):
+        g.advance_board()
+        for i in range(4):
+            b[i], c = slo.advance_board(b[i], 0.3, seed=2, env=i, counter=int(ctr[i]))
+            ctr[i] = c
+        assert (g.board.cpu().numpy() == b).all(), t

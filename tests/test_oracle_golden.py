@@ -123,3 +123,37 @@ def _counter_after_episode(d, i):
         env.step([a])
     assert (env.boards[0] == d["final_board_%d" % i]).all()
     return int(env.states[0]["rng_counter"])
+
+
+def _obs_cases():
+    d = gu.load("obs.npz")
+    for i in range(int(d["n_cases"])):
+        yield i, d
+
+
+def test_get_obs_golden():
+    """oracle get_obs (numpy) replayed along the reference traces of tests/golden/obs.npz"""
+    for i, d in _obs_cases():
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        one = gu.level_slice(lv, l0, l0 + 1)
+        env = slo.OracleBatchEnv(slo.OraclePool(**one), [0], seed=int(d["seed_%d" % i]),
+                                 env_id0=int(d["env_%d" % i]))
+        view = tuple(int(v) for v in d["view_%d" % i])
+        ch = tuple(int(c) for c in d["channels_%d" % i]) or None
+        kw = dict(view_shape=view, remove_white_goals=bool(d["remove_white_%d" % i]), output_channels=ch)
+
+        def obs():
+            st = env.states[0]
+            return slo.get_obs(env.boards[0], env.goals[0], (st["agent_x"], st["agent_y"]),
+                               one["board"][0], **kw)
+
+        want = d["obs_%d" % i]
+        assert (obs() == want[0]).all(), (i, "reset")
+        k = 1
+        for t, a in enumerate(d["actions_%d" % i]):
+            env.step([a])
+            if (t + 1) % int(d["every_%d" % i]) == 0:
+                assert (obs() == want[k]).all(), (i, t)
+                k += 1
+        assert k == len(want)
