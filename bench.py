@@ -89,6 +89,7 @@ def cpu_arm(n_envs, steps, warmup, threads):
     kind = "port"
     if slo.have_ref():
         slo.use_reference_advance(True)
+        kind = "reference"  # advance_board is the reference's own C (oracle/_ref); the rule code around it is the port
     env = slo.OracleBatchEnv(slo.OraclePool(**lv), np.arange(n_envs) % 100, seed=0, threads=threads)
     rng = np.random.RandomState(2)
     acts = rng.randint(9, size=(steps + warmup, n_envs))
@@ -213,21 +214,40 @@ def run_b200(args):
     ms = distributed.max_over_ranks(ms, dev)
     clocks = sampler.summary()
 
-    # ---- e2e: host-buffer step through the public API (pinned host actions in, reward/done out) ----
-    e2e_steps = min(K, 500)
+    # ---- e2e: host-buffer steps through the public API (SafeLifeEnv.step_host -> slb_env_step_host*) ----
+    # Every step copies that step's actions from pinned host memory to the device, runs the fused step
+    # and copies reward + done back to pinned host memory.  Two independent env batches are kept in
+    # flight on two streams (the double-buffered actor loop: while one batch's results travel back, the
+    # next batch steps); each step's outputs are waited for before that batch's buffers are reused.
+    e2e_steps = min(K, 1000)
+    depth = 2
     h_act = torch.from_numpy(rng.randint(9, size=(n_act, n)).astype(np.uint8)).pin_memory()
-    h_rew = torch.zeros(n, dtype=torch.int32).pin_memory()
-    h_done = torch.zeros(n, dtype=torch.uint8).pin_memory()
-    for i in range(3):
-        envs[i % ring].step_host(h_act[i % n_act], h_rew, h_done)
+    h_out = [torch.zeros(5 * n, dtype=torch.uint8).pin_memory() for _ in range(depth)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]
+    a_ptr = [h_act[k].data_ptr() for k in range(n_act)]
+    o_ptr = [(o.data_ptr(), o.data_ptr() + 4 * n) for o in h_out]
     torch.cuda.synchronize()
+
+    def e2e_loop(count):
+        for i in range(count):
+            s = i % depth
+            if i >= depth:
+                envs[i % ring].wait(streams[s])  # outputs of step i - depth are now in h_out[s]
+            envs[i % ring].step_host(a_ptr[i % n_act], o_ptr[s][0], o_ptr[s][1], sync=False, stream=streams[s])
+        for s in range(depth):
+            envs[0].wait(streams[s])
+
+    e2e_loop(2 * depth + 2)
     if world > 1:
         torch.distributed.barrier()
     t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        envs[i % ring].step_host(h_act[i % n_act], h_rew, h_done)
-    torch.cuda.synchronize()
+    e2e_loop(e2e_steps)
     e2e_s = distributed.max_over_ranks(time.perf_counter() - t0, dev)
+    # the same, strictly one step at a time (launch, wait, read), for reference
+    t0 = time.perf_counter()
+    for i in range(200):
+        envs[i % ring].step_host(a_ptr[i % n_act], o_ptr[0][0], o_ptr[0][1])
+    e2e_serial_s = distributed.max_over_ranks(time.perf_counter() - t0, dev) / 200
 
     if rank != 0:
         return
@@ -250,15 +270,21 @@ def run_b200(args):
                      "bytes_per_env_step": BYTES_PER_ENV_STEP, "kernel": "res_env_rollout_kernel, T=1 (per launch: %d envs)" % n},
         "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": n,
                 "d2h_bytes_per_step": 5 * n, "steps": e2e_steps,
-                "what": "slb_env_step_host: pinned uint8 actions H2D, fused step, int32 reward + uint8 done D2H, sync"},
+                "what": "SafeLifeEnv.step_host -> slb_env_step_host_async: per step pinned uint8 actions H2D, fused step, "
+                        "int32 reward + uint8 done D2H to pinned memory; 2 independent batches in flight on 2 streams",
+                "serial_value": n * world / e2e_serial_s,
+                "serial_what": "one step at a time: copy in, step, copy out, wait"},
         "stats_allreduce": distributed.stats_dict(stats),
     }
     # CPU baseline on this box's host cores, bounded sample (rank 0, N=1 only)
     if world == 1 and not args.no_cpu:
         threads = len(os.sched_getaffinity(0))
-        v, dt, kind, physics = cpu_arm(n, 10, 2, threads)
+        v0, dt0, _, _ = cpu_arm(n, 20, 2, threads)          # calibrate, then ~10 s of CPU work
+        cpu_steps = int(min(20000, max(50, 10.0 / (dt0 / 20))))
+        v, dt, kind, physics = cpu_arm(n, cpu_steps, 2, threads)
         line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": threads, "kind": kind,
-                                "sample": "10 steps of the same 4096-env batch (%.1f s); physics = %s, rules = C port" % (dt, physics)}
+                                "sample": "%d steps of the same %d-env batch (%.1f s of wall clock on %d threads); "
+                                          "physics = %s, rules = C port of safelife_game.py" % (cpu_steps, n, dt, threads, physics)}
     print(json.dumps(line))
 
 
@@ -277,7 +303,7 @@ def main():
         args.warmup = args.warmup if args.warmup is not None else 2
         run_reference(args)
     else:
-        args.steps = args.steps if args.steps is not None else 2000
+        args.steps = args.steps if args.steps is not None else 100000
         args.warmup = args.warmup if args.warmup is not None else 50
         run_b200(args)
 

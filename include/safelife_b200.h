@@ -183,6 +183,16 @@ int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                       int auto_reset_stride, void *stream);
 
+/* The same without the final wait: H2D copy, step and D2H copy are queued on `stream` (give steps that
+ * should overlap their own streams; at most 8 streams per calling thread); the host buffers must be
+ * page-locked for the copies to be asynchronous and are valid after slb_stream_wait(stream). */
+int slb_env_step_host_async(const slb_pool *pool, int n, void *d_board, void *d_goals,
+                            slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
+                            uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
+                            int auto_reset_stride, void *stream);
+/* Low-latency wait for everything queued on `stream` (spins on cudaStreamQuery). */
+int slb_stream_wait(void *stream);
+
 /* ---- A13/A14: side_effect_score up to the EMD (side_effects.py:59-141) ---------------------------
  * For episode i: b0 = d_board0[i] advanced d_num_steps[i] times, then num_samples paired steps of
  * b0 (inaction, draws first) and b1 = d_board1[i] (action); per-cell-type count maps.

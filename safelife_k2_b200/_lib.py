@@ -57,6 +57,8 @@ SYMBOLS = {
     "slb_env_step": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _vp]),
     "slb_env_rollout": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _i, _u64, _u64, _vp, _vp, _i, _vp]),
     "slb_env_step_host": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _vp]),
+    "slb_env_step_host_async": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _vp]),
+    "slb_stream_wait": (_i, [_vp]),
     "slb_side_effect_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _vp, _u64, _u64, _vp, _i, _vp,
                                     _vp, _vp, _vp, _vp]),
     "slb_accumulate_stats": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),

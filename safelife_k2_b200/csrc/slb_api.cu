@@ -380,33 +380,70 @@ int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
 }
 
 
+// One device staging block per (calling thread, stream), grown on demand:
+// [reward 4n | done n | pad | actions n].  Steps in flight on different streams never share one.
+namespace {
+struct HostIo { cudaStream_t st; uint8_t *d; size_t cap; };
+int host_io_block(cudaStream_t st, size_t need, uint8_t **out) {
+    thread_local HostIo slots[8] = {};
+    thread_local int used = 0;
+    HostIo *s = nullptr;
+    for (int k = 0; k < used; k++)
+        if (slots[k].st == st) s = &slots[k];
+    if (!s) {
+        if (used == 8) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 8 streams per thread");
+        s = &slots[used++];
+        s->st = st; s->d = nullptr; s->cap = 0;
+    }
+    if (need > s->cap) {
+        if (s->d) cudaFree(s->d);
+        s->d = nullptr; s->cap = 0;
+        SLB_CUDA(cudaMalloc(&s->d, need));
+        s->cap = need;
+    }
+    *out = s->d;
+    return SLB_OK;
+}
+}  // namespace
+
+int slb_env_step_host_async(const slb_pool *pool, int n, void *d_board, void *d_goals,
+                            slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
+                            uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
+                            int auto_reset_stride, void *stream) {
+    if (n < 0 || !h_actions) return fail(SLB_ERR_INVALID, "slb_env_step_host: bad arguments");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t off_done = (size_t)4 * n, off_act = ((size_t)5 * n + 15) & ~(size_t)15;
+    uint8_t *d_io = nullptr;
+    if (int rc = host_io_block(st, off_act + (size_t)n, &d_io)) return rc;
+    SLB_CUDA(cudaMemcpyAsync(d_io + off_act, h_actions, (size_t)n, cudaMemcpyHostToDevice, st));
+    int rc = slb_env_step(pool, n, d_board, d_goals, d_state, d_io + off_act, time_limit, seed, env_id0,
+                          (int32_t *)d_io, d_io + off_done, auto_reset_stride, stream);
+    if (rc) return rc;
+    if (h_reward && h_done == (uint8_t *)(h_reward + n)) {  // adjacent host outputs: one copy
+        SLB_CUDA(cudaMemcpyAsync(h_reward, d_io, (size_t)5 * n, cudaMemcpyDeviceToHost, st));
+    } else {
+        if (h_done) SLB_CUDA(cudaMemcpyAsync(h_done, d_io + off_done, (size_t)n, cudaMemcpyDeviceToHost, st));
+        if (h_reward) SLB_CUDA(cudaMemcpyAsync(h_reward, d_io, (size_t)4 * n, cudaMemcpyDeviceToHost, st));
+    }
+    return SLB_OK;
+}
+
 int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
                       uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                       int auto_reset_stride, void *stream) {
-    if (n < 0 || !h_actions) return fail(SLB_ERR_INVALID, "slb_env_step_host: bad arguments");
-    if (n == 0) return SLB_OK;
-    cudaStream_t st = (cudaStream_t)stream;
-    // one staging block per calling thread, grown on demand: [actions n | done n | pad | reward 4n]
-    thread_local uint8_t *d_io = nullptr;
-    thread_local size_t d_io_cap = 0;
-    size_t off_done = (size_t)n, off_rew = ((size_t)2 * n + 15) & ~(size_t)15;
-    size_t need = off_rew + (size_t)4 * n;
-    if (need > d_io_cap) {
-        if (d_io) cudaFree(d_io);
-        d_io = nullptr;
-        d_io_cap = 0;
-        SLB_CUDA(cudaMalloc(&d_io, need));
-        d_io_cap = need;
-    }
-    SLB_CUDA(cudaMemcpyAsync(d_io, h_actions, (size_t)n, cudaMemcpyHostToDevice, st));
-    int rc = slb_env_step(pool, n, d_board, d_goals, d_state, d_io, time_limit, seed, env_id0,
-                          (int32_t *)(d_io + off_rew), d_io + off_done, auto_reset_stride, stream);
-    if (rc) return rc;
-    if (h_done) SLB_CUDA(cudaMemcpyAsync(h_done, d_io + off_done, (size_t)n, cudaMemcpyDeviceToHost, st));
-    if (h_reward)
-        SLB_CUDA(cudaMemcpyAsync(h_reward, d_io + off_rew, (size_t)4 * n, cudaMemcpyDeviceToHost, st));
-    SLB_CUDA(cudaStreamSynchronize(st));
+    if (int rc = slb_env_step_host_async(pool, n, d_board, d_goals, d_state, h_actions, time_limit, seed,
+                                         env_id0, h_reward, h_done, auto_reset_stride, stream))
+        return rc;
+    return slb_stream_wait(stream);
+}
+
+int slb_stream_wait(void *stream) {
+    // spin on the stream instead of a blocking wait: a step takes a few microseconds
+    cudaError_t q;
+    while ((q = cudaStreamQuery((cudaStream_t)stream)) == cudaErrorNotReady) {}
+    if (q != cudaSuccess) return fail(SLB_ERR_CUDA, "stream wait: %s", cudaGetErrorString(q));
     return SLB_OK;
 }
 

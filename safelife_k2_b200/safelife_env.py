@@ -18,6 +18,10 @@ from . import _lib
 from .safelife_game import ACTION_NAMES, LevelPool, SafeLifeGame
 
 
+def _hptr(x):
+    return x if isinstance(x, int) or x is None else _lib.ptr(x)
+
+
 class _Info(dict):
     """The step's info dict (safelife_env.py:176-186).  'board' and 'goals' are uint16 [N,H,W]
     tensors exported from the resident state when first asked for, not on every step."""
@@ -70,6 +74,7 @@ class SafeLifeEnv(object):
         self.num_envs = int(self.num_envs)
         self._seed = 0
         self._lib = _lib.load()
+        self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
         dev = self.pool.device
         self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
         self._done = torch.zeros(self.num_envs, dtype=torch.uint8, device=dev)
@@ -162,16 +167,26 @@ class SafeLifeEnv(object):
         })
         return (self.get_obs() if self.compute_obs else None), self._reward, done, info
 
-    def step_host(self, actions_host, reward_host, done_host):
-        """Host-buffer step through slb_env_step_host: uint8 actions in (pinned) host memory in,
-        int32 rewards / uint8 dones out; board state stays resident on the device.  Synchronous."""
+    def step_host(self, actions_host, reward_host, done_host, sync=True, stream=None):
+        """Host-buffer step (slb_env_step_host): uint8 actions in host memory in, int32 rewards / uint8
+        dones out; board state stays resident on the device.  Pass raw pointers (ints) or tensors /
+        arrays.  sync=False only queues the copies and the step on `stream` (a torch stream; default the
+        current one) — call wait(stream) before reading the outputs; independent env batches stepped on
+        different streams overlap."""
         g = self.game
-        with torch.cuda.device(self.pool.device):
-            _lib.check(self._lib.slb_env_step_host(
-                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                _lib.ptr(actions_host), int(self.time_limit), g.seed, g.env_id0,
-                _lib.ptr(reward_host), _lib.ptr(done_host),
-                self._stride() if self.auto_reset else 0, _lib.current_stream()))
+        if torch.cuda.current_device() != self._dev_index:
+            torch.cuda.set_device(self._dev_index)
+        st = (stream if stream is not None else torch.cuda.current_stream()).cuda_stream
+        fn = self._lib.slb_env_step_host if sync else self._lib.slb_env_step_host_async
+        rc = fn(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+                _hptr(actions_host), self.time_limit, g.seed, g.env_id0, _hptr(reward_host),
+                _hptr(done_host), self._stride() if self.auto_reset else 0, st)
+        if rc:
+            _lib.check(rc)
+
+    def wait(self, stream=None):
+        st = (stream if stream is not None else torch.cuda.current_stream()).cuda_stream
+        _lib.check(self._lib.slb_stream_wait(st))
 
     def rollout(self, actions, reward=None, done=None):
         """T fused steps with pre-staged actions: uint8 [T,N] cuda tensor.  Returns (reward int32
