@@ -32,6 +32,17 @@ BYTES_PER_ENV_STEP = 8 * H * W + 32  # 4 B per cell-update, bo
 L2_BYTES = 126 * 1024 * 1024
 
 
+def load_traffic(n):
+    """DRAM bytes per launch of the step kernel from the committed ncu capture (only valid for the
+    configuration it was captured on: 4096 envs)."""
+    p = os.path.join(ROOT, "profiles", "r01", "traffic.json")
+    if n != ENVS_PER_GPU or not os.path.exists(p):
+        return None, None
+    with open(p) as f:
+        t = json.load(f)
+    return t["dram_bytes_read_per_launch"] + t["dram_bytes_write_per_launch"], t["note"]
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -254,6 +265,7 @@ def run_b200(args):
     value = n * world * K / (ms * 1e-3)
     peak, peak_src = load_peaks()
     achieved = n * BYTES_PER_ENV_STEP / (ms * 1e-3 / K) / 1e9
+    traffic, traffic_note = load_traffic(n)
     line = {
         "metric": "env_steps_per_s", "value": value, "unit": "env-steps/s", "n_gpus": world,
         "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
@@ -266,7 +278,9 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
+                     "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else peak_src,
+                     "algorithmic_bytes_per_launch": n * BYTES_PER_ENV_STEP,
                      "bytes_per_env_step": BYTES_PER_ENV_STEP, "kernel": "res_env_rollout_kernel, T=1 (per launch: %d envs)" % n},
         "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": n,
                 "d2h_bytes_per_step": 5 * n, "steps": e2e_steps,
