@@ -320,6 +320,9 @@ def main():
         args.steps = args.steps if args.steps is not None else 100000
         args.warmup = args.warmup if args.warmup is not None else 50
         run_b200(args)
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
 
 
 if __name__ == "__main__":
