@@ -7,6 +7,7 @@
 
 #include "slb_fast.cuh"
 #include "slb_generic_env.cuh"
+#include "slb_big.cuh"
 
 using namespace slb;
 
@@ -55,7 +56,7 @@ int check_pool(const slb_pool *p) {
     if (!p->board || !p->goals || !p->agent_x || !p->agent_y || !p->orientation ||
         !p->spawn_prob || !p->min_performance || !p->baseline || !p->exit_mask || !p->plane_bits)
         return fail(SLB_ERR_INVALID, "pool has NULL arrays");
-    if (fast_shape(p->h, p->w) && (!p->board_res || !p->goals_res))
+    if ((fast_shape(p->h, p->w) || big_shape(p->h, p->w)) && (!p->board_res || !p->goals_res))
         return fail(SLB_ERR_INVALID, "pool.board_res / goals_res are required for %dx%d boards", p->h, p->w);
     return check_shape(0, p->h, p->w);
 }
@@ -80,6 +81,24 @@ int allow_smem(K kernel, size_t bytes) {
     return 0;
 }
 
+// launches the big-board env kernel with the stages in a.ops
+int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
+    const size_t bytes = big_smem_bytes(pool->h, pool->w);
+    if (int rc = allow_smem(big_env_kernel, bytes)) return rc;
+    big_env_kernel<<<a.n, BIG_THREADS, bytes, st>>>(*pool, a);
+    return SLB_OK;
+}
+
+BigArgs big_args(int n, void *board, void *goals, slb_env_state *state, int ops) {
+    BigArgs a = {};
+    a.board = (uint32_t *)board;
+    a.goals = (uint32_t *)goals;
+    a.state = state;
+    a.n = n;
+    a.ops = ops;
+    return a;
+}
+
 }  // namespace
 
 extern "C" {
@@ -90,7 +109,9 @@ uint64_t slb_launch_count(void) { return g_launches.load(); }
 
 size_t slb_resident_bytes(int h, int w) {
     if (h < 3 || w < 3) return 0;
-    return fast_shape(h, w) ? resident_words(h) * 4 : (size_t)h * w * 2;
+    if (fast_shape(h, w)) return resident_words(h) * 4;
+    if (big_shape(h, w)) return (size_t)64 * h * (w / 32);
+    return (size_t)h * w * 2;
 }
 
 static int refresh_groups(slb_pool *pool, cudaStream_t st) {
@@ -111,6 +132,14 @@ int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int 
     uint32_t *pool_plane_bits = pool ? pool->plane_bits + which : nullptr;
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (big_shape(h, w)) {
+        if ((uintptr_t)d_res % 16 || (uintptr_t)d_cells % 16)
+            return fail(SLB_ERR_INVALID, "resident buffers and cell arrays must be 16-byte aligned");
+        big_import_kernel<<<n, 256, 0, st>>>(d_cells, (uint32_t *)d_res, h, w, pool_plane_bits);
+        SLB_LAUNCHED();
+        if (pool) return refresh_groups(pool, st);
+        return SLB_OK;
+    }
     if (!fast_shape(h, w)) {
         SLB_CUDA(cudaMemcpyAsync(d_res, d_cells, (size_t)n * h * w * 2, cudaMemcpyDeviceToDevice, st));
         return SLB_OK;
@@ -128,6 +157,13 @@ int slb_resident_export(const void *d_res, uint16_t *d_cells, int n, int h, int 
     if (!d_cells || !d_res) return fail(SLB_ERR_INVALID, "slb_resident_export: NULL pointer");
     if (n == 0) return SLB_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (big_shape(h, w)) {
+        if ((uintptr_t)d_res % 16 || (uintptr_t)d_cells % 16)
+            return fail(SLB_ERR_INVALID, "resident buffers and cell arrays must be 16-byte aligned");
+        big_export_kernel<<<n, 256, 0, st>>>((const uint32_t *)d_res, d_cells, h, w);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
     if (!fast_shape(h, w)) {
         SLB_CUDA(cudaMemcpyAsync(d_cells, d_res, (size_t)n * h * w * 2, cudaMemcpyDeviceToDevice, st));
         return SLB_OK;
@@ -143,7 +179,7 @@ int slb_pool_prepare(slb_pool *pool, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     pool_prepare_kernel<<<pool->n_levels, GEN_THREADS, 0, (cudaStream_t)stream>>>(*pool);
     SLB_LAUNCHED();
-    if (fast_shape(pool->h, pool->w)) {
+    if (fast_shape(pool->h, pool->w) || big_shape(pool->h, pool->w)) {
         if (int rc = slb_resident_import(pool->board, pool->board_res, pool->n_levels, pool->h, pool->w,
                                          pool, 0, stream)) return rc;
         if (int rc = slb_resident_import(pool->goals, pool->goals_res, pool->n_levels, pool->h, pool->w,
@@ -240,10 +276,15 @@ int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const
     if (n < 0 || !d_level_ids || !d_board || !d_goals || !d_state)
         return fail(SLB_ERR_INVALID, "slb_env_reset: bad arguments");
     if (n == 0) return SLB_OK;
-    if (fast_shape(pool->h, pool->w))
+    if (fast_shape(pool->h, pool->w)) {
         res_reset_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(*pool, n, d_level_ids, d_mask,
                                                               (uint32_t *)d_board, (uint32_t *)d_goals, d_state);
-    else
+    } else if (big_shape(pool->h, pool->w)) {
+        BigArgs a = big_args(n, d_board, d_goals, d_state, BIG_RESET);
+        a.level_ids = d_level_ids;
+        a.mask = d_mask;
+        if (int rc = launch_big(pool, a, (cudaStream_t)stream)) return rc;
+    } else
         reset_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
             *pool, d_level_ids, d_mask, (uint16_t *)d_board, (uint16_t *)d_goals, d_state);
     SLB_LAUNCHED();
@@ -256,10 +297,15 @@ int slb_execute_action(const slb_pool *pool, int n, void *d_board, slb_env_state
     if (n < 0 || !d_board || !d_state || !d_actions)
         return fail(SLB_ERR_INVALID, "slb_execute_action: bad arguments");
     if (n == 0) return SLB_OK;
-    if (fast_shape(pool->h, pool->w))
+    if (fast_shape(pool->h, pool->w)) {
         res_action_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(*pool, n, (uint32_t *)d_board, d_state,
                                                                d_actions, d_reward);
-    else
+    } else if (big_shape(pool->h, pool->w)) {
+        BigArgs a = big_args(n, d_board, nullptr, d_state, BIG_ACTION);
+        a.actions = d_actions;
+        a.reward_out = d_reward;
+        if (int rc = launch_big(pool, a, (cudaStream_t)stream)) return rc;
+    } else
         execute_action_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
             (uint16_t *)d_board, n, pool->h, pool->w, d_state, d_actions, d_reward);
     SLB_LAUNCHED();
@@ -276,6 +322,11 @@ int slb_game_advance(const slb_pool *pool, int n, void *d_board, void *d_goals,
     if (fast_shape(pool->h, pool->w)) {
         res_advance_kernel<<<RES_GRID(n), st>>>(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals,
                                                d_state, seed, env_id0);
+    } else if (big_shape(pool->h, pool->w)) {
+        BigArgs a = big_args(n, d_board, d_goals, d_state, BIG_PHYSICS);
+        a.seed = seed;
+        a.env_id0 = env_id0;
+        if (int rc = launch_big(pool, a, st)) return rc;
     } else {
         size_t bytes = (size_t)pool->h * pool->w * 2;
         if (bytes + kSmemStatic > smem_optin())
@@ -300,7 +351,11 @@ int slb_points_and_performance(const slb_pool *pool, int n, const void *d_board,
         res_score_kernel<false><<<RES_GRID(n), (cudaStream_t)stream>>>(
             *pool, n, (uint32_t *)d_board, (const uint32_t *)d_goals, (slb_env_state *)d_state, d_points,
             d_completed, d_possible, d_can_exit);
-    else
+    else if (big_shape(pool->h, pool->w)) {
+        BigArgs a = big_args(n, (void *)d_board, (void *)d_goals, (slb_env_state *)d_state, BIG_POINTS);
+        a.points = d_points; a.completed = d_completed; a.possible = d_possible; a.can_exit = d_can_exit;
+        if (int rc = launch_big(pool, a, (cudaStream_t)stream)) return rc;
+    } else
         points_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
             *pool, (const uint16_t *)d_board, (const uint16_t *)d_goals, d_state, d_points, d_completed,
             d_possible, d_can_exit);
@@ -317,7 +372,10 @@ int slb_update_exit_colors(const slb_pool *pool, int n, void *d_board, const voi
     if (fast_shape(pool->h, pool->w))
         res_score_kernel<true><<<RES_GRID(n), (cudaStream_t)stream>>>(
             *pool, n, (uint32_t *)d_board, (const uint32_t *)d_goals, d_state, nullptr, nullptr, nullptr, nullptr);
-    else
+    else if (big_shape(pool->h, pool->w)) {
+        BigArgs a = big_args(n, d_board, (void *)d_goals, d_state, BIG_PAINT);
+        if (int rc = launch_big(pool, a, (cudaStream_t)stream)) return rc;
+    } else
         exit_colors_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
             *pool, (uint16_t *)d_board, (const uint16_t *)d_goals, d_state);
     SLB_LAUNCHED();
@@ -338,6 +396,14 @@ int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
             return fail(SLB_ERR_UNSUPPORTED, "too many envs per launch (resident word offsets are 32-bit)");
         launch_res_env_rollout(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions, 1,
                                time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, st);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    if (big_shape(pool->h, pool->w)) {
+        BigArgs a = big_args(n, d_board, d_goals, d_state, BIG_ACTION | BIG_PHYSICS | BIG_BOOK);
+        a.actions = d_actions; a.time_limit = time_limit; a.seed = seed; a.env_id0 = env_id0;
+        a.reward_out = d_reward; a.done_out = d_done; a.auto_reset_stride = auto_reset_stride;
+        if (int rc = launch_big(pool, a, st)) return rc;
         SLB_LAUNCHED();
         return SLB_OK;
     }
@@ -508,6 +574,10 @@ int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_
         res_obs_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(
             *pool, n, (const uint32_t *)d_board, (const uint32_t *)d_goals, d_state, vh, vw,
             remove_white_goals, d_obs);
+    else if (big_shape(pool->h, pool->w))
+        big_obs_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(*pool, (const uint32_t *)d_board,
+                                                          (const uint32_t *)d_goals, d_state, vh, vw,
+                                                          remove_white_goals, d_obs);
     else
         get_obs_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
             *pool, (const uint16_t *)d_board, (const uint16_t *)d_goals, d_state, vh, vw,

@@ -1,0 +1,630 @@
+// slb_big.cuh — resident bit-plane kernels for boards larger than one warp's 32x32 (e.g. the 256x256
+// scaling configuration): W a multiple of 32, one CTA per env.
+//
+// Resident layout of one board (64*H*(W/32) bytes, same as the small layout with rows widened to
+// W/32 words): 4 plane groups x H rows x (W/32) words x uint4; "item" = one 32-cell word of a row,
+// item index = row * wpr + word, so consecutive threads read consecutive uint4.
+//
+// One advance_board step: phase A writes the 11 neighbourhood SOURCE planes of the whole board into
+// shared memory (alive; preserving, inhibiting, spawning; alive & {D2, r, g, b}; spawning & {r, g,
+// b}); after one barrier every item reads the 3x3 words around it, aligns the left/right neighbours
+// with one funnel shift each and reduces the nine words with carry-save adders.  Results go
+// straight back to the resident planes in global memory (an item's planes are only ever read and
+// written by its own thread; neighbours come from the shared snapshot).  Spawn draws need the
+// raster-order rank of every eligible cell of the board: eligible words are parked in shared
+// memory, scanned CTA-wide, and a fix-up pass applies the successful draws.
+#pragma once
+#include "slb_resident.cuh"
+
+namespace slb {
+
+constexpr int BIG_THREADS = 512;
+constexpr int BIG_SRC = 11;  // source planes in shared memory
+constexpr size_t BIG_SMEM_LIMIT = 200 * 1024;
+
+__host__ __device__ inline size_t big_smem_bytes(int h, int w) {
+    const size_t items = (size_t)h * (w / 32);
+    return (BIG_SRC + 1) * items * 4 + (size_t)h * 4;  // sources + eligible words + row flags
+}
+
+inline bool big_shape(int h, int w) {
+    return !fast_shape(h, w) && h >= 3 && w >= 32 && (w % 32) == 0 && big_smem_bytes(h, w) <= BIG_SMEM_LIMIT;
+}
+
+struct BigGeo {
+    int h, wpr, items;
+};
+
+__device__ __forceinline__ void big_load(const uint32_t *__restrict__ base, const BigGeo &g, int item,
+                                         unsigned groups, uint32_t P[16]) {
+    const uint4 *b4 = reinterpret_cast<const uint4 *>(base);
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    const uint4 q0 = b4[item];
+    const uint4 q1 = b4[g.items + item];
+    const uint4 q2 = (groups & 4u) ? b4[2 * g.items + item] : z;
+    const uint4 q3 = (groups & 8u) ? b4[3 * g.items + item] : z;
+    P[0] = q0.x; P[4] = q0.y; P[9] = q0.z; P[10] = q0.w;
+    P[11] = q1.x; P[3] = q1.y; P[2] = q1.z; P[15] = q1.w;
+    P[1] = q2.x; P[5] = q2.y; P[6] = q2.z; P[8] = q2.w;
+    P[7] = q3.x; P[12] = q3.y; P[13] = q3.z; P[14] = q3.w;
+}
+
+__device__ __forceinline__ void big_store(uint32_t *__restrict__ base, const BigGeo &g, int item,
+                                          unsigned groups, const uint32_t P[16]) {
+    uint4 *b4 = reinterpret_cast<uint4 *>(base);
+    b4[item] = make_uint4(P[0], P[4], P[9], P[10]);
+    b4[g.items + item] = make_uint4(P[11], P[3], P[2], P[15]);
+    if (groups & 4u) b4[2 * g.items + item] = make_uint4(P[1], P[5], P[6], P[8]);
+    if (groups & 8u) b4[3 * g.items + item] = make_uint4(P[7], P[12], P[13], P[14]);
+}
+
+// the nine words of source plane `s` around an item, neighbours aligned to the item's columns
+struct Nine {
+    uint32_t ul, um, ur, ml, mm, mr, dl, dm, dr;
+};
+
+struct BigNbr {
+    int up, mid, dn;  // item offsets of the three rows
+    int j, jl, jr;    // word index and its toroidal neighbours
+};
+
+__device__ __forceinline__ Nine gather9(const uint32_t *__restrict__ s, const BigNbr &nb) {
+    Nine n;
+    uint32_t l, m, r;
+    l = s[nb.up + nb.jl]; m = s[nb.up + nb.j]; r = s[nb.up + nb.jr];
+    n.ul = __funnelshift_l(l, m, 1); n.um = m; n.ur = __funnelshift_r(m, r, 1);
+    l = s[nb.mid + nb.jl]; m = s[nb.mid + nb.j]; r = s[nb.mid + nb.jr];
+    n.ml = __funnelshift_l(l, m, 1); n.mm = m; n.mr = __funnelshift_r(m, r, 1);
+    l = s[nb.dn + nb.jl]; m = s[nb.dn + nb.j]; r = s[nb.dn + nb.jr];
+    n.dl = __funnelshift_l(l, m, 1); n.dm = m; n.dr = __funnelshift_r(m, r, 1);
+    return n;
+}
+
+__device__ __forceinline__ uint32_t nine_or(const Nine &n) {
+    return or3(or3(n.ul, n.um, n.ur), or3(n.ml, n.mm, n.mr), or3(n.dl, n.dm, n.dr));
+}
+
+// >= 2 of the nine
+__device__ __forceinline__ uint32_t nine_two(const Nine &n) {
+    const uint32_t su = xor3(n.ul, n.um, n.ur), cu = maj3(n.ul, n.um, n.ur);
+    const uint32_t sm = xor3(n.ml, n.mm, n.mr), cm = maj3(n.ml, n.mm, n.mr);
+    const uint32_t sd = xor3(n.dl, n.dm, n.dr), cd = maj3(n.dl, n.dm, n.dr);
+    return or3(cu, cm, cd) | maj3(su, sm, sd);
+}
+
+// n == 3 / n == 4 of the nine (n = s + 2 c summed over the three rows)
+__device__ __forceinline__ void nine_count(const Nine &n, uint32_t &is3, uint32_t &is4) {
+    const uint32_t su = xor3(n.ul, n.um, n.ur), cu = maj3(n.ul, n.um, n.ur);
+    const uint32_t sm = xor3(n.ml, n.mm, n.mr), cm = maj3(n.ml, n.mm, n.mr);
+    const uint32_t sd = xor3(n.dl, n.dm, n.dr), cd = maj3(n.dl, n.dm, n.dr);
+    const uint32_t t0 = xor3(su, sm, sd), t1 = maj3(su, sm, sd);  // ones: t0 + 2 t1
+    const uint32_t u0 = xor3(cu, cm, cd), u1 = maj3(cu, cm, cd);  // twos: u0 + 2 u1
+    const uint32_t n1 = t1 ^ u0, k = t1 & u0, n2 = u1 ^ k;        // n = t0 + 2 n1 + 4 n2 + 8 (u1 & k)
+    is3 = t0 & n1 & ~n2;
+    is4 = ~t0 & ~n1 & n2;
+}
+
+// CTA-wide exclusive prefix sum of one int per thread (thread order); total returned to all.
+__device__ __forceinline__ int big_scan(int v, int *warp_tot, int &total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(FULL, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    int before = 0, tot = 0;
+    for (int k = 0; k < nw; k++) {
+        const int t = warp_tot[k];
+        if (k < wid) before += t;
+        tot += t;
+    }
+    __syncthreads();
+    total = tot;
+    return before + incl - v;
+}
+
+struct BigSmem {
+    uint32_t *src;    // [BIG_SRC][items]
+    uint32_t *elig;   // [items]
+    uint32_t *rowf;   // [h]: bit 0 row has preserving|inhibiting, bit 1 row has spawning
+    int *warp_tot;    // [BIG_THREADS / 32]
+};
+
+// ---------------------------------------------------------------------------------------------
+// One advance_board step of the CTA's board, in place on its resident planes (advance_board.c:34-120,
+// closed form of SURVEY Appendix A; same lazy-but-exact evaluation as physics_planes, per item).
+// Every thread of the CTA must call.  Returns the env's updated draw counter (same in all threads).
+// ---------------------------------------------------------------------------------------------
+__device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsigned groups,
+                                       const BigSmem &sm, float spawn_prob, uint64_t seed, uint64_t env,
+                                       uint64_t counter) {
+    const int T = blockDim.x;
+    // ---- phase A: snapshot of the source planes ----
+    for (int r = threadIdx.x; r < g.h; r += T) sm.rowf[r] = 0u;
+    __syncthreads();
+    int has7 = 0;
+    for (int it = threadIdx.x; it < g.items; it += T) {
+        uint32_t P[16];
+        big_load(planes, g, it, groups, P);
+        const uint32_t a = P[0], sp = P[7];
+        uint32_t *s = sm.src + it;
+        s[0] = a;
+        s[1 * g.items] = P[5];
+        s[2 * g.items] = P[6];
+        s[3 * g.items] = sp;
+        s[4 * g.items] = a & (P[3] | P[8]);  // D2 = destructible | exit (advance_board.c:44-46)
+        s[5 * g.items] = a & P[9];
+        s[6 * g.items] = a & P[10];
+        s[7 * g.items] = a & P[11];
+        s[8 * g.items] = sp & P[9];
+        s[9 * g.items] = sp & P[10];
+        s[10 * g.items] = sp & P[11];
+        const uint32_t f = ((P[5] | P[6]) ? 1u : 0u) | (sp ? 2u : 0u);
+        if (f) atomicOr(&sm.rowf[it / g.wpr], f);
+        has7 |= sp != 0u;
+    }
+    const int any7 = __syncthreads_or(has7);  // also the barrier between the phases
+    // ---- phase B: rule per item ----
+    for (int it = threadIdx.x; it < g.items; it += T) {
+        const int r = it / g.wpr, j = it - r * g.wpr;
+        BigNbr nb;
+        const int ru = (r == 0) ? g.h - 1 : r - 1, rd = (r == g.h - 1) ? 0 : r + 1;
+        nb.up = ru * g.wpr; nb.mid = r * g.wpr; nb.dn = rd * g.wpr;
+        nb.j = j; nb.jl = (j == 0) ? g.wpr - 1 : j - 1; nb.jr = (j == g.wpr - 1) ? 0 : j + 1;
+        const uint32_t rf = sm.rowf[ru] | sm.rowf[r] | sm.rowf[rd];
+        uint32_t P[16];
+        big_load(planes, g, it, groups, P);
+        const uint32_t a = P[0], fz = P[4];
+        uint32_t is3, is4;
+        nine_count(gather9(sm.src, nb), is3, is4);
+        const uint32_t die0 = a & ~(fz | is3 | is4);
+        const uint32_t open0 = ~(a | fz);
+        uint32_t PR = 0, IH = 0;
+        if (rf & 1u) {
+            PR = nine_or(gather9(sm.src + 1 * g.items, nb));
+            IH = nine_or(gather9(sm.src + 2 * g.items, nb));
+        }
+        const uint32_t die = die0 & ~PR;
+        const uint32_t open = open0 & ~IH;
+        const uint32_t birth = open & is3;
+        uint32_t elig = 0;
+        if (rf & 2u) elig = open & ~is3 & nine_or(gather9(sm.src + 3 * g.items, nb));
+        if (any7) sm.elig[it] = elig;
+        const uint32_t flip = die | birth;
+        if (flip) {
+            uint32_t nD = 0, nR = 0, nG = 0, nB = 0;
+            if (birth) {
+                nD = birth & nine_two(gather9(sm.src + 4 * g.items, nb));
+                uint32_t tR = nine_two(gather9(sm.src + 5 * g.items, nb));
+                uint32_t tG = nine_two(gather9(sm.src + 6 * g.items, nb));
+                uint32_t tB = nine_two(gather9(sm.src + 7 * g.items, nb));
+                if (rf & 2u) {
+                    tR |= nine_or(gather9(sm.src + 8 * g.items, nb));
+                    tG |= nine_or(gather9(sm.src + 9 * g.items, nb));
+                    tB |= nine_or(gather9(sm.src + 10 * g.items, nb));
+                }
+                nR = birth & tR; nG = birth & tG; nB = birth & tB;
+            }
+            const uint32_t keep = ~flip;
+#pragma unroll
+            for (int b = 0; b < 16; b++) P[b] &= keep;
+            P[0] |= birth; P[3] |= nD; P[9] |= nR; P[10] |= nG; P[11] |= nB;
+            big_store(planes, g, it, groups, P);
+        }
+    }
+    if (!any7) return counter;  // uniform
+    // ---- spawn draws: raster-order rank of every eligible cell, then the fix-up ----
+    __syncthreads();
+    const uint64_t thr = spawn_threshold(spawn_prob);
+    for (int base = 0; base < g.items; base += T) {  // uniform trip count
+        const int it = base + threadIdx.x;
+        const uint32_t elig = (it < g.items) ? sm.elig[it] : 0u;
+        int total;
+        const int rank = big_scan(__popc(elig), sm.warp_tot, total);
+        if (elig) {
+            uint64_t idx = counter + (uint64_t)rank;
+            uint32_t e = elig, spawn = 0;
+            while (e) {
+                const uint32_t bit = e & (0u - e);
+                e ^= bit;
+                if (stream_u53(seed, env, idx) < thr) spawn |= bit;
+                idx++;
+            }
+            if (spawn) {
+                const int r = it / g.wpr, j = it - r * g.wpr;
+                BigNbr nb;
+                const int ru = (r == 0) ? g.h - 1 : r - 1, rd = (r == g.h - 1) ? 0 : r + 1;
+                nb.up = ru * g.wpr; nb.mid = r * g.wpr; nb.dn = rd * g.wpr;
+                nb.j = j; nb.jl = (j == 0) ? g.wpr - 1 : j - 1; nb.jr = (j == g.wpr - 1) ? 0 : j + 1;
+                const uint32_t tR = nine_two(gather9(sm.src + 5 * g.items, nb)) | nine_or(gather9(sm.src + 8 * g.items, nb));
+                const uint32_t tG = nine_two(gather9(sm.src + 6 * g.items, nb)) | nine_or(gather9(sm.src + 9 * g.items, nb));
+                const uint32_t tB = nine_two(gather9(sm.src + 7 * g.items, nb)) | nine_or(gather9(sm.src + 10 * g.items, nb));
+                uint32_t P[16];
+                big_load(planes, g, it, groups, P);
+                const uint32_t keep = ~spawn;  // spawned cells were dead: their residue bits are discarded
+#pragma unroll
+                for (int b = 0; b < 16; b++) P[b] &= keep;
+                P[0] |= spawn; P[3] |= spawn;  // always destructible (advance_board.c:110-114)
+                P[9] |= spawn & tR; P[10] |= spawn & tG; P[11] |= spawn & tB;
+                big_store(planes, g, it, groups, P);
+            }
+        }
+        counter += (uint64_t)total;
+    }
+    __syncthreads();
+    return counter;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Single cells of a resident big board, for execute_action: lane p < 16 owns plane p, a warp vote
+// assembles / scatters the uint16 cell value.  Called by all 32 lanes of ONE warp.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int plane_word(int p, int item, int items) {
+    const int idx = (int)((0x7FED432BCA915680ull >> (4 * p)) & 15ull);  // plane -> group * 4 + slot
+    return ((idx >> 2) * items + item) * 4 + (idx & 3);
+}
+
+__device__ __forceinline__ uint32_t big_cell_read(const uint32_t *planes, const BigGeo &g, int x, int y) {
+    const int lane = threadIdx.x & 31;
+    uint32_t bit = 0;
+    if (lane < 16) bit = (planes[plane_word(lane, y * g.wpr + (x >> 5), g.items)] >> (x & 31)) & 1u;
+    return __ballot_sync(FULL, bit != 0u) & 0xffffu;
+}
+
+__device__ __forceinline__ void big_cell_write(uint32_t *planes, const BigGeo &g, unsigned groups, int x,
+                                               int y, uint32_t v) {
+    const int lane = threadIdx.x & 31;
+    if (lane < 16) {
+        const int idx = (int)((0x7FED432BCA915680ull >> (4 * lane)) & 15ull);
+        if ((groups >> (idx >> 2)) & 1u) {
+            uint32_t *w = planes + plane_word(lane, y * g.wpr + (x >> 5), g.items);
+            const uint32_t m = 1u << (x & 31);
+            *w = (*w & ~m) | (((v >> lane) & 1u) ? m : 0u);
+        }
+    }
+    __syncwarp();
+}
+
+// execute_action (safelife_game.py:347-393, move_agent :308-345), literal read / write order like
+// execute_action_cells, on single cells of the resident planes.  One warp.
+__device__ inline int big_action(uint32_t *b, const BigGeo &g, unsigned groups, int w, int &ax, int &ay,
+                                 int &orientation, int &game_over, int action, int can_exit) {
+    if (game_over || action < 1 || action > 8) return 0;
+    const int h = g.h;
+    const int dir = (action - 1) & 3;
+    orientation = dir;
+    const int fx = (dir & 1) ? 2 - dir : 0, fy = (dir & 1) ? 0 : dir - 1;
+    const int x0 = ax, y0 = ay;
+    const int x1 = (x0 + fx + w) % w, y1 = (y0 + fy + h) % h;
+    int reward = 0;
+    if (action <= 4) {
+        const int x2 = (x0 - fx + w) % w, y2 = (y0 - fy + h) % h;
+        bool moved = false;
+        const uint32_t front = big_cell_read(b, g, x1, y1);
+        if (front == 0) {
+            big_cell_write(b, g, groups, x1, y1, big_cell_read(b, g, x0, y0));
+            big_cell_write(b, g, groups, x0, y0, 0);
+            moved = true;
+        } else if ((front & EXIT) && can_exit) {
+            game_over = 1;
+            reward = 1;
+        } else if (front & PUSHABLE) {
+            const int x3 = (x0 + 2 * fx + 2 * w) % w, y3 = (y0 + 2 * fy + 2 * h) % h;
+            const uint32_t far = big_cell_read(b, g, x3, y3);
+            if (far == 0) {
+                big_cell_write(b, g, groups, x3, y3, front);
+                big_cell_write(b, g, groups, x1, y1, big_cell_read(b, g, x0, y0));
+                big_cell_write(b, g, groups, x0, y0, 0);
+                moved = true;
+            } else if (far & EXIT) {
+                big_cell_write(b, g, groups, x1, y1, big_cell_read(b, g, x0, y0));
+                big_cell_write(b, g, groups, x0, y0, 0);
+                moved = true;
+            }
+        }
+        if (moved) {
+            ax = x1;
+            ay = y1;
+            const uint32_t behind = big_cell_read(b, g, x2, y2);
+            if (behind & PULLABLE) {
+                big_cell_write(b, g, groups, x0, y0, behind);
+                big_cell_write(b, g, groups, x2, y2, 0);
+            }
+        }
+    } else {
+        const uint32_t pc = big_cell_read(b, g, x0, y0) & COLORS;
+        const uint32_t t = big_cell_read(b, g, x1, y1);
+        if (t == 0)
+            big_cell_write(b, g, groups, x1, y1, ALIVE | DESTRUCTIBLE | pc);
+        else if (t & DESTRUCTIBLE)
+            big_cell_write(b, g, groups, x1, y1, 0);
+    }
+    return reward;
+}
+
+// ---------------------------------------------------------------------------------------------
+// score / paint / reset passes over the CTA's env.  Every thread of the CTA must call.
+// ---------------------------------------------------------------------------------------------
+// block reduction of three ints; scratch: 96 ints
+__device__ __forceinline__ void big_sum3(int &a, int &b, int &c, int *scratch) {
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();
+    if (lane == 0) { scratch[wid] = a; scratch[32 + wid] = b; scratch[64 + wid] = c; }
+    __syncthreads();
+    int ra = 0, rb = 0, rc = 0;
+    for (int k = 0; k < nw; k++) { ra += scratch[k]; rb += scratch[32 + k]; rc += scratch[64 + k]; }
+    a = ra; b = rb; c = rc;
+    __syncthreads();
+}
+
+// current_points / performance_ratio sums (safelife_game.py:590-631); skip_exits: cells of the exit
+// mask e0 count as dead (what they are once painted)
+__device__ inline void big_score(const uint32_t *board, const uint32_t *goals, const BigGeo &g,
+                                 const uint32_t *e0, bool skip_exits, int *scratch, int &pts, int &cur,
+                                 int &pos) {
+    Geo full;
+    full.h = g.h; full.w = 32; full.up = full.dn = 0; full.wmask = 0xffffffffu; full.row = true;
+    pts = cur = pos = 0;
+    for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
+        uint32_t B[16], G[16];
+        big_load(board, g, it, 3u, B);  // every plane the score reads lives in groups 0 / 1
+        big_load(goals, g, it, 3u, G);
+        if (skip_exits) B[0] &= ~e0[it];
+        const RowScore rs = score_planes(B, G, full);
+        pts += rs.points; cur += rs.current; pos += rs.possible;
+    }
+    big_sum3(pts, cur, pos, scratch);
+}
+
+// update_exit_colors' repaint (safelife_game.py:531-537)
+__device__ inline void big_paint(uint32_t *board, const BigGeo &g, unsigned groups, const uint32_t *e0,
+                                 int can_exit) {
+    for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
+        const uint32_t m = e0[it];
+        if (!m) continue;
+        uint32_t P[16];
+        big_load(board, g, it, groups, P);
+#pragma unroll
+        for (int b = 0; b < 16; b++) P[b] &= ~m;
+        P[4] |= m; P[8] |= m;
+        if (can_exit) P[9] |= m;
+        big_store(board, g, it, groups, P);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The env kernel for big boards: one CTA per env; `ops` selects the stages (the fused step is
+// ACTION | PHYSICS | BOOK; the single stages serve SafeLifeGame's method-by-method API).
+// ---------------------------------------------------------------------------------------------
+enum : int { BIG_RESET = 1, BIG_ACTION = 2, BIG_PHYSICS = 4, BIG_BOOK = 8, BIG_POINTS = 16, BIG_PAINT = 32 };
+
+struct BigArgs {
+    uint32_t *board, *goals;
+    slb_env_state *state;
+    const uint8_t *actions;
+    const int32_t *level_ids;
+    const uint8_t *mask;
+    int32_t *reward_out;
+    uint8_t *done_out;
+    int32_t *points, *completed, *possible;
+    uint8_t *can_exit;
+    uint64_t seed, env_id0;
+    int n, time_limit, auto_reset_stride, ops;
+};
+
+// load level `level` into the env (safelife_env.py:188-198); fills the warp-0-owned scalars in *st
+__device__ inline void big_reset(const slb_pool &pool, int level, const BigGeo &g, unsigned gb, unsigned gg,
+                                 uint32_t *board, uint32_t *goals, slb_env_state *st, int *scratch) {
+    const size_t words = (size_t)16 * g.items;
+    const uint4 *b0 = reinterpret_cast<const uint4 *>((const uint32_t *)pool.board_res + level * words);
+    const uint4 *g0 = reinterpret_cast<const uint4 *>((const uint32_t *)pool.goals_res + level * words);
+    uint4 *b4 = reinterpret_cast<uint4 *>(board), *g4 = reinterpret_cast<uint4 *>(goals);
+    for (int k = threadIdx.x; k < 4 * g.items; k += blockDim.x) {
+        const unsigned grp = 1u << (k / g.items);
+        if (gb & grp) b4[k] = b0[k];
+        if (gg & grp) g4[k] = g0[k];
+    }
+    __syncthreads();
+    const uint32_t *e0 = pool.exit_mask + (size_t)level * g.items;
+    int pts, cur, pos;
+    big_score(board, goals, g, e0, true, scratch, pts, cur, pos);  // points as they are once painted
+    const int baseline = pool.baseline[level];
+    const int completed = cur - baseline, possible = pos - baseline;
+    const int ce = can_exit_rule(pool.min_performance[level], completed, possible);
+    big_paint(board, g, gb, e0, ce);
+    if (threadIdx.x == 0) {
+        st->agent_x = pool.agent_x[level]; st->agent_y = pool.agent_y[level];
+        st->orientation = pool.orientation[level];
+        st->game_over = 0; st->num_steps = 0; st->level_id = level; st->episode_length = 0;
+        st->episode_completed = 0; st->old_points = pts; st->can_exit = ce; st->completed = completed;
+        st->possible = possible; st->episode_reward = 0;
+        // rng_counter deliberately untouched: the stream keeps running across episodes
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(BIG_THREADS, 2)
+big_env_kernel(slb_pool pool, BigArgs a) {
+    extern __shared__ __align__(16) uint32_t big_smem[];
+    __shared__ int scratch[96];
+    __shared__ int warp_tot[BIG_THREADS / 32];
+    __shared__ int sh_act[5];
+    const int i = blockIdx.x;
+    BigGeo g;
+    g.h = pool.h; g.wpr = pool.w / 32; g.items = g.h * g.wpr;
+    BigSmem sm;
+    sm.src = big_smem;
+    sm.elig = big_smem + (size_t)BIG_SRC * g.items;
+    sm.rowf = sm.elig + g.items;
+    sm.warp_tot = warp_tot;
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
+    const size_t words = (size_t)16 * g.items;
+    uint32_t *board = a.board + i * words, *goals = a.goals ? a.goals + i * words : nullptr;
+    slb_env_state *st = a.state + i;
+    const int ops = a.ops;
+
+    if (ops & BIG_RESET) {
+        if (a.mask && !a.mask[i]) return;
+        big_reset(pool, a.level_ids[i], g, gb, gg, board, goals, st, scratch);
+        return;
+    }
+    const int level = st->level_id;
+    const uint64_t env = a.env_id0 + (uint64_t)i;
+    int act_reward = 0;
+    if (ops & BIG_ACTION) {
+        if (threadIdx.x < 32) {
+            int ax = st->agent_x, ay = st->agent_y, o = st->orientation, go = st->game_over;
+            const int r = big_action(board, g, gb, pool.w, ax, ay, o, go, a.actions[i], st->can_exit);
+            if (threadIdx.x == 0) { sh_act[0] = ax; sh_act[1] = ay; sh_act[2] = o; sh_act[3] = go; sh_act[4] = r; }
+        }
+        __syncthreads();
+        act_reward = sh_act[4];
+        if (threadIdx.x == 0) {
+            st->agent_x = sh_act[0]; st->agent_y = sh_act[1]; st->orientation = sh_act[2]; st->game_over = sh_act[3];
+            if (!(ops & BIG_BOOK) && a.reward_out) a.reward_out[i] = act_reward;
+        }
+    }
+    uint64_t counter = st->rng_counter;
+    if (ops & BIG_PHYSICS) {
+        const float p = pool.spawn_prob[level];
+        // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
+        counter = big_physics(board, g, gb, sm, p, a.seed, env, counter);
+        __syncthreads();
+        counter = big_physics(goals, g, gg, sm, p, a.seed, env, counter);
+        __syncthreads();
+        if (threadIdx.x == 0) { st->rng_counter = counter; st->num_steps += 1; }
+    }
+    if (!(ops & (BIG_BOOK | BIG_POINTS | BIG_PAINT))) return;
+    const uint32_t *e0 = pool.exit_mask + (size_t)level * g.items;
+    int pts, cur, pos;
+    big_score(board, goals, g, e0, false, scratch, pts, cur, pos);
+    const int baseline = pool.baseline[level];
+    const int completed = cur - baseline, possible = pos - baseline;
+    const int ce = can_exit_rule(pool.min_performance[level], completed, possible);
+    if (ops & BIG_POINTS) {
+        if (threadIdx.x == 0) {
+            if (a.points) a.points[i] = pts;
+            if (a.completed) a.completed[i] = completed;
+            if (a.possible) a.possible[i] = possible;
+            if (a.can_exit) a.can_exit[i] = (uint8_t)ce;
+        }
+        return;
+    }
+    big_paint(board, g, gb, e0, ce);
+    __shared__ int sh_done;
+    if (threadIdx.x == 0) {
+        st->can_exit = ce; st->completed = completed; st->possible = possible;
+        if (ops & BIG_BOOK) {
+            const int reward = act_reward + pts - st->old_points;
+            const int ep_len = st->episode_length + 1;
+            const int done = (ep_len > a.time_limit) || st->game_over;
+            st->episode_length = ep_len;
+            st->episode_completed = done;
+            st->old_points = pts;
+            st->episode_reward += reward;
+            if (a.reward_out) a.reward_out[i] = reward;
+            if (a.done_out) a.done_out[i] = (uint8_t)done;
+            sh_done = done;
+        }
+    }
+    if (!(ops & BIG_BOOK)) return;
+    __syncthreads();
+    if (a.auto_reset_stride > 0 && sh_done)
+        big_reset(pool, (level + a.auto_reset_stride) % pool.n_levels, g, gb, gg, board, goals, st, scratch);
+}
+
+// ---------------------------------------------------------------------------------------------
+// cells <-> resident planes for big boards (API boundary); grid = N, one item per thread per pass.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+big_import_kernel(const uint16_t *__restrict__ cells, uint32_t *planes, int h, int w, uint32_t *plane_bits) {
+    BigGeo g;
+    g.h = h; g.wpr = w / 32; g.items = h * g.wpr;
+    const uint4 *src = reinterpret_cast<const uint4 *>(cells + (size_t)blockIdx.x * h * w);  // 64 B per item
+    uint32_t *dst = planes + (size_t)blockIdx.x * 16 * g.items;
+    uint32_t bits = 0;
+    for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
+        uint32_t x[16], P[16];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 v = src[it * 4 + q];
+            x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
+        }
+        cells_to_planes(x, P);
+        big_store(dst, g, it, 15u, P);
+#pragma unroll
+        for (int b = 0; b < 16; b++) bits |= (P[b] != 0u) ? (1u << b) : 0u;
+    }
+    if (plane_bits) {
+        bits = __reduce_or_sync(FULL, bits);
+        if ((threadIdx.x & 31) == 0 && (bits & ~*plane_bits)) atomicOr(plane_bits, bits);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+big_export_kernel(const uint32_t *__restrict__ planes, uint16_t *cells, int h, int w) {
+    BigGeo g;
+    g.h = h; g.wpr = w / 32; g.items = h * g.wpr;
+    const uint32_t *src = planes + (size_t)blockIdx.x * 16 * g.items;
+    uint4 *dst = reinterpret_cast<uint4 *>(cells + (size_t)blockIdx.x * h * w);
+    for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
+        uint32_t x[16], P[16];
+        big_load(src, g, it, 15u, P);
+        planes_to_cells(P, x);
+#pragma unroll
+        for (int q = 0; q < 4; q++) dst[it * 4 + q] = make_uint4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
+    }
+}
+
+// get_obs from resident big boards (safelife_env.py:125-155, helper_utils.py:41-74): one thread per
+// view cell gathers its 16 plane bits.  grid = N.
+__device__ __forceinline__ uint32_t big_cell_value(const uint32_t *planes, const BigGeo &g, int x, int y) {
+    const int item = y * g.wpr + (x >> 5), sh = x & 31;
+    uint32_t v = 0;
+#pragma unroll
+    for (int p = 0; p < 16; p++) v |= ((planes[plane_word(p, item, g.items)] >> sh) & 1u) << p;
+    return v;
+}
+
+__global__ void __launch_bounds__(256)
+big_obs_kernel(slb_pool pool, const uint32_t *__restrict__ board, const uint32_t *__restrict__ goals,
+               const slb_env_state *__restrict__ state, int vh, int vw, int remove_white, uint16_t *obs) {
+    BigGeo g;
+    g.h = pool.h; g.wpr = pool.w / 32; g.items = g.h * g.wpr;
+    const int i = blockIdx.x, h = pool.h, w = pool.w;
+    const uint32_t *b = board + (size_t)i * 16 * g.items, *gl = goals + (size_t)i * 16 * g.items;
+    const int x0 = state[i].agent_x, y0 = state[i].agent_y, level = state[i].level_id;
+    const int x1 = x0 - vw / 2, y1 = y0 - vh / 2;
+    uint16_t *o = obs + (size_t)i * vh * vw;
+    for (int k = threadIdx.x; k < vh * vw; k += blockDim.x) {
+        const int vy = k / vw, vx = k - vy * vw;
+        const int y = pymod_w(y1 + vy, h), x = pymod_w(x1 + vx, w);
+        uint32_t gv = big_cell_value(gl, g, x, y) & COLORS;
+        if (remove_white && gv == COLORS) gv = 0;
+        o[k] = (uint16_t)(big_cell_value(b, g, x, y) + (gv << 3));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t *em = pool.exit_mask + (size_t)level * g.items;
+        for (int it = 0; it < g.items; it++) {
+            uint32_t m = em[it];
+            while (m) {
+                const int y = it / g.wpr, x = (it - y * g.wpr) * 32 + __ffs(m) - 1;
+                m &= m - 1;
+                int jy = pymod_w(y - y0 + h / 2, h) - h / 2;
+                int jx = pymod_w(x - x0 + w / 2, w) - w / 2;
+                jy = min(max(jy + vh / 2, 0), vh - 1);
+                jx = min(max(jx + vw / 2, 0), vw - 1);
+                uint32_t gv = big_cell_value(gl, g, x, y) & COLORS;
+                if (remove_white && gv == COLORS) gv = 0;
+                o[jy * vw + jx] = (uint16_t)(big_cell_value(b, g, x, y) + (gv << 3));
+            }
+        }
+    }
+}
+
+}  // namespace slb

@@ -302,11 +302,13 @@ def _random_levels(rng, p, h, w, exits=2):
             "spawn_prob": rng.choice([0.0, 0.3, 1.0], size=p), "min_performance": rng.choice([-1.0, 0.0, 0.01], size=p)}
 
 
-@pytest.mark.parametrize("h,w", [(4, 4), (5, 7), (26, 26), (32, 32), (31, 9), (9, 31), (3, 5), (40, 33)])
+@pytest.mark.parametrize("h,w", [(4, 4), (5, 7), (26, 26), (32, 32), (31, 9), (9, 31), (3, 5), (40, 33),
+                                  (3, 32), (36, 32), (40, 64), (64, 96)])
 def test_action_stress_vs_oracle(sl, h, w):
     """Random actions on dense random levels of odd shapes (toroidal push / pull / exit / toggle at the
-    seams, spawners, auto-reset): full state equality with the oracle every few steps.  Shapes outside
-    4..32 take the uint16-resident generic kernels, the others the resident bit-plane kernels."""
+    seams, spawners, auto-reset): full state equality with the oracle every few steps.  4..32 squares take
+    the warp-per-env bit-plane kernels, widths that are multiples of 32 the CTA-per-env bit-plane kernels
+    (slb_big.cuh), everything else the uint16-resident generic kernels."""
     rng = np.random.RandomState(h * 100 + w)
     lv = _random_levels(rng, 24, h, w)
     n, steps = 96, 60
@@ -351,7 +353,7 @@ def test_resident_import_export_roundtrip(sl):
     board imported into a game with bits its pool had never seen is stepped correctly afterwards."""
     rng = np.random.RandomState(3)
     L = sl.lib.load()
-    for h, w in [(26, 26), (4, 32), (32, 4), (17, 23), (40, 5)]:
+    for h, w in [(26, 26), (4, 32), (32, 4), (17, 23), (40, 5), (40, 64), (256, 256), (3, 32)]:
         cells = torch.from_numpy(rng.randint(0, 1 << 16, size=(50, h, w)).astype(np.uint16)).cuda()
         res = torch.zeros(50 * L.slb_resident_bytes(h, w), dtype=torch.uint8, device="cuda")
         back = torch.zeros_like(cells)
