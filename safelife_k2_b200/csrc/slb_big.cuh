@@ -33,7 +33,20 @@ inline bool big_shape(int h, int w) {
 
 struct BigGeo {
     int h, wpr, items;
+    int wshift;  // log2(wpr) when wpr is a power of two, else -1
 };
+
+__device__ __forceinline__ BigGeo big_geo(int h, int w) {
+    BigGeo g;
+    g.h = h; g.wpr = w / 32; g.items = h * g.wpr;
+    g.wshift = (g.wpr & (g.wpr - 1)) ? -1 : __ffs(g.wpr) - 1;
+    return g;
+}
+
+__device__ __forceinline__ void big_row_word(const BigGeo &g, int item, int &r, int &j) {
+    if (g.wshift >= 0) { r = item >> g.wshift; j = item & (g.wpr - 1); }
+    else { r = item / g.wpr; j = item - r * g.wpr; }
+}
 
 __device__ __forceinline__ void big_load(const uint32_t *__restrict__ base, const BigGeo &g, int item,
                                          unsigned groups, uint32_t P[16]) {
@@ -63,19 +76,33 @@ struct Nine {
     uint32_t ul, um, ur, ml, mm, mr, dl, dm, dr;
 };
 
+// The shared snapshot is item-major: word k of item i at src[i * BIG_SRC + k] (BIG_SRC is odd, so
+// consecutive items hit different banks); the nine neighbour items are addressed once per item and
+// every source plane is an immediate offset from them.
 struct BigNbr {
-    int up, mid, dn;  // item offsets of the three rows
-    int j, jl, jr;    // word index and its toroidal neighbours
+    const uint32_t *ul, *um, *ur, *ml, *mm, *mr, *dl, *dm, *dr;
 };
 
-__device__ __forceinline__ Nine gather9(const uint32_t *__restrict__ s, const BigNbr &nb) {
+__device__ __forceinline__ BigNbr big_nbr(const uint32_t *src, const BigGeo &g, int r, int j) {
+    const int ru = (r == 0) ? g.h - 1 : r - 1, rd = (r == g.h - 1) ? 0 : r + 1;
+    const int jl = (j == 0) ? g.wpr - 1 : j - 1, jr = (j == g.wpr - 1) ? 0 : j + 1;
+    const int up = ru * g.wpr, mid = r * g.wpr, dn = rd * g.wpr;
+    BigNbr nb;
+    nb.ul = src + (up + jl) * BIG_SRC; nb.um = src + (up + j) * BIG_SRC; nb.ur = src + (up + jr) * BIG_SRC;
+    nb.ml = src + (mid + jl) * BIG_SRC; nb.mm = src + (mid + j) * BIG_SRC; nb.mr = src + (mid + jr) * BIG_SRC;
+    nb.dl = src + (dn + jl) * BIG_SRC; nb.dm = src + (dn + j) * BIG_SRC; nb.dr = src + (dn + jr) * BIG_SRC;
+    return nb;
+}
+
+template <int K>
+__device__ __forceinline__ Nine gather9(const BigNbr &nb) {
     Nine n;
     uint32_t l, m, r;
-    l = s[nb.up + nb.jl]; m = s[nb.up + nb.j]; r = s[nb.up + nb.jr];
+    l = nb.ul[K]; m = nb.um[K]; r = nb.ur[K];
     n.ul = __funnelshift_l(l, m, 1); n.um = m; n.ur = __funnelshift_r(m, r, 1);
-    l = s[nb.mid + nb.jl]; m = s[nb.mid + nb.j]; r = s[nb.mid + nb.jr];
+    l = nb.ml[K]; m = nb.mm[K]; r = nb.mr[K];
     n.ml = __funnelshift_l(l, m, 1); n.mm = m; n.mr = __funnelshift_r(m, r, 1);
-    l = s[nb.dn + nb.jl]; m = s[nb.dn + nb.j]; r = s[nb.dn + nb.jr];
+    l = nb.dl[K]; m = nb.dm[K]; r = nb.dr[K];
     n.dl = __funnelshift_l(l, m, 1); n.dm = m; n.dr = __funnelshift_r(m, r, 1);
     return n;
 }
@@ -150,61 +177,63 @@ __device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsign
         uint32_t P[16];
         big_load(planes, g, it, groups, P);
         const uint32_t a = P[0], sp = P[7];
-        uint32_t *s = sm.src + it;
+        uint32_t *s = sm.src + it * BIG_SRC;
         s[0] = a;
-        s[1 * g.items] = P[5];
-        s[2 * g.items] = P[6];
-        s[3 * g.items] = sp;
-        s[4 * g.items] = a & (P[3] | P[8]);  // D2 = destructible | exit (advance_board.c:44-46)
-        s[5 * g.items] = a & P[9];
-        s[6 * g.items] = a & P[10];
-        s[7 * g.items] = a & P[11];
-        s[8 * g.items] = sp & P[9];
-        s[9 * g.items] = sp & P[10];
-        s[10 * g.items] = sp & P[11];
+        s[1] = P[5];
+        s[2] = P[6];
+        s[3] = sp;
+        s[4] = a & (P[3] | P[8]);  // D2 = destructible | exit (advance_board.c:44-46)
+        s[5] = a & P[9];
+        s[6] = a & P[10];
+        s[7] = a & P[11];
+        s[8] = sp & P[9];
+        s[9] = sp & P[10];
+        s[10] = sp & P[11];
         const uint32_t f = ((P[5] | P[6]) ? 1u : 0u) | (sp ? 2u : 0u);
-        if (f) atomicOr(&sm.rowf[it / g.wpr], f);
+        if (f) {
+            int r, j;
+            big_row_word(g, it, r, j);
+            atomicOr(&sm.rowf[r], f);
+        }
         has7 |= sp != 0u;
     }
     const int any7 = __syncthreads_or(has7);  // also the barrier between the phases
     // ---- phase B: rule per item ----
     for (int it = threadIdx.x; it < g.items; it += T) {
-        const int r = it / g.wpr, j = it - r * g.wpr;
-        BigNbr nb;
-        const int ru = (r == 0) ? g.h - 1 : r - 1, rd = (r == g.h - 1) ? 0 : r + 1;
-        nb.up = ru * g.wpr; nb.mid = r * g.wpr; nb.dn = rd * g.wpr;
-        nb.j = j; nb.jl = (j == 0) ? g.wpr - 1 : j - 1; nb.jr = (j == g.wpr - 1) ? 0 : j + 1;
-        const uint32_t rf = sm.rowf[ru] | sm.rowf[r] | sm.rowf[rd];
+        int r, j;
+        big_row_word(g, it, r, j);
+        const BigNbr nb = big_nbr(sm.src, g, r, j);
+        const uint32_t rf = sm.rowf[(r == 0) ? g.h - 1 : r - 1] | sm.rowf[r] | sm.rowf[(r == g.h - 1) ? 0 : r + 1];
         uint32_t P[16];
         big_load(planes, g, it, groups, P);
         const uint32_t a = P[0], fz = P[4];
         uint32_t is3, is4;
-        nine_count(gather9(sm.src, nb), is3, is4);
+        nine_count(gather9<0>(nb), is3, is4);
         const uint32_t die0 = a & ~(fz | is3 | is4);
         const uint32_t open0 = ~(a | fz);
         uint32_t PR = 0, IH = 0;
         if (rf & 1u) {
-            PR = nine_or(gather9(sm.src + 1 * g.items, nb));
-            IH = nine_or(gather9(sm.src + 2 * g.items, nb));
+            PR = nine_or(gather9<1>(nb));
+            IH = nine_or(gather9<2>(nb));
         }
         const uint32_t die = die0 & ~PR;
         const uint32_t open = open0 & ~IH;
         const uint32_t birth = open & is3;
         uint32_t elig = 0;
-        if (rf & 2u) elig = open & ~is3 & nine_or(gather9(sm.src + 3 * g.items, nb));
+        if (rf & 2u) elig = open & ~is3 & nine_or(gather9<3>(nb));
         if (any7) sm.elig[it] = elig;
         const uint32_t flip = die | birth;
         if (flip) {
             uint32_t nD = 0, nR = 0, nG = 0, nB = 0;
             if (birth) {
-                nD = birth & nine_two(gather9(sm.src + 4 * g.items, nb));
-                uint32_t tR = nine_two(gather9(sm.src + 5 * g.items, nb));
-                uint32_t tG = nine_two(gather9(sm.src + 6 * g.items, nb));
-                uint32_t tB = nine_two(gather9(sm.src + 7 * g.items, nb));
+                nD = birth & nine_two(gather9<4>(nb));
+                uint32_t tR = nine_two(gather9<5>(nb));
+                uint32_t tG = nine_two(gather9<6>(nb));
+                uint32_t tB = nine_two(gather9<7>(nb));
                 if (rf & 2u) {
-                    tR |= nine_or(gather9(sm.src + 8 * g.items, nb));
-                    tG |= nine_or(gather9(sm.src + 9 * g.items, nb));
-                    tB |= nine_or(gather9(sm.src + 10 * g.items, nb));
+                    tR |= nine_or(gather9<8>(nb));
+                    tG |= nine_or(gather9<9>(nb));
+                    tB |= nine_or(gather9<10>(nb));
                 }
                 nR = birth & tR; nG = birth & tG; nB = birth & tB;
             }
@@ -216,46 +245,67 @@ __device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsign
         }
     }
     if (!any7) return counter;  // uniform
-    // ---- spawn draws: raster-order rank of every eligible cell, then the fix-up ----
+    // ---- spawn draws ----
+    // (1) raster-order rank of every eligible cell: CTA-wide scan over the items' popcounts; the ranks
+    //     are parked in source slot 0 of each item (the count / flag sources are dead after phase B);
+    // (2) the draws counter .. counter + total - 1 are evaluated by ALL threads, one draw per lane, a
+    //     warp vote packing 32 outcomes into one word of a bit stream (source slot 1 of item w);
+    // (3) every item with eligible cells pulls its popcount bits out of the stream and applies them.
     __syncthreads();
-    const uint64_t thr = spawn_threshold(spawn_prob);
+    int total = 0;
     for (int base = 0; base < g.items; base += T) {  // uniform trip count
         const int it = base + threadIdx.x;
-        const uint32_t elig = (it < g.items) ? sm.elig[it] : 0u;
-        int total;
-        const int rank = big_scan(__popc(elig), sm.warp_tot, total);
-        if (elig) {
-            uint64_t idx = counter + (uint64_t)rank;
-            uint32_t e = elig, spawn = 0;
-            while (e) {
-                const uint32_t bit = e & (0u - e);
-                e ^= bit;
-                if (stream_u53(seed, env, idx) < thr) spawn |= bit;
-                idx++;
-            }
-            if (spawn) {
-                const int r = it / g.wpr, j = it - r * g.wpr;
-                BigNbr nb;
-                const int ru = (r == 0) ? g.h - 1 : r - 1, rd = (r == g.h - 1) ? 0 : r + 1;
-                nb.up = ru * g.wpr; nb.mid = r * g.wpr; nb.dn = rd * g.wpr;
-                nb.j = j; nb.jl = (j == 0) ? g.wpr - 1 : j - 1; nb.jr = (j == g.wpr - 1) ? 0 : j + 1;
-                const uint32_t tR = nine_two(gather9(sm.src + 5 * g.items, nb)) | nine_or(gather9(sm.src + 8 * g.items, nb));
-                const uint32_t tG = nine_two(gather9(sm.src + 6 * g.items, nb)) | nine_or(gather9(sm.src + 9 * g.items, nb));
-                const uint32_t tB = nine_two(gather9(sm.src + 7 * g.items, nb)) | nine_or(gather9(sm.src + 10 * g.items, nb));
-                uint32_t P[16];
-                big_load(planes, g, it, groups, P);
-                const uint32_t keep = ~spawn;  // spawned cells were dead: their residue bits are discarded
-#pragma unroll
-                for (int b = 0; b < 16; b++) P[b] &= keep;
-                P[0] |= spawn; P[3] |= spawn;  // always destructible (advance_board.c:110-114)
-                P[9] |= spawn & tR; P[10] |= spawn & tG; P[11] |= spawn & tB;
-                big_store(planes, g, it, groups, P);
-            }
+        const int cnt = (it < g.items) ? __popc(sm.elig[it]) : 0;
+        int chunk_total;
+        const int rank = big_scan(cnt, sm.warp_tot, chunk_total);
+        if (it < g.items) sm.src[it * BIG_SRC] = (uint32_t)(total + rank);
+        total += chunk_total;
+    }
+    if (total == 0) return counter;  // uniform
+    {
+        const uint64_t thr = spawn_threshold(spawn_prob);
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = T >> 5;
+        for (int w0 = warp; w0 * 32 < total; w0 += nwarps) {
+            const int d = w0 * 32 + lane;
+            const bool hit = d < total && stream_u53(seed, env, counter + (uint64_t)d) < thr;
+            const uint32_t word = __ballot_sync(FULL, hit);
+            if (lane == 0) sm.src[w0 * BIG_SRC + 1] = word;
         }
-        counter += (uint64_t)total;
     }
     __syncthreads();
-    return counter;
+    for (int it = threadIdx.x; it < g.items; it += T) {
+        uint32_t e = sm.elig[it];
+        if (!e) continue;
+        const uint32_t rank = sm.src[it * BIG_SRC];
+        const int w0 = (int)(rank >> 5), nw = (total + 31) >> 5;
+        const uint32_t lo = sm.src[w0 * BIG_SRC + 1];
+        const uint32_t hi = (w0 + 1 < nw) ? sm.src[(w0 + 1) * BIG_SRC + 1] : 0u;
+        uint32_t bits = __funnelshift_r(lo, hi, rank & 31u);  // this item's outcomes, first eligible cell in bit 0
+        uint32_t spawn = 0;
+        while (e) {
+            const uint32_t bit = e & (0u - e);
+            e ^= bit;
+            if (bits & 1u) spawn |= bit;
+            bits >>= 1;
+        }
+        if (!spawn) continue;
+        int r, j;
+        big_row_word(g, it, r, j);
+        const BigNbr nb = big_nbr(sm.src, g, r, j);
+        const uint32_t tR = nine_two(gather9<5>(nb)) | nine_or(gather9<8>(nb));
+        const uint32_t tG = nine_two(gather9<6>(nb)) | nine_or(gather9<9>(nb));
+        const uint32_t tB = nine_two(gather9<7>(nb)) | nine_or(gather9<10>(nb));
+        uint32_t P[16];
+        big_load(planes, g, it, groups, P);
+        const uint32_t keep = ~spawn;  // spawned cells were dead: their residue bits are discarded
+#pragma unroll
+        for (int b = 0; b < 16; b++) P[b] &= keep;
+        P[0] |= spawn; P[3] |= spawn;  // always destructible (advance_board.c:110-114)
+        P[9] |= spawn & tR; P[10] |= spawn & tG; P[11] |= spawn & tB;
+        big_store(planes, g, it, groups, P);
+    }
+    __syncthreads();
+    return counter + (uint64_t)total;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -454,8 +504,7 @@ big_env_kernel(slb_pool pool, BigArgs a) {
     __shared__ int warp_tot[BIG_THREADS / 32];
     __shared__ int sh_act[5];
     const int i = blockIdx.x;
-    BigGeo g;
-    g.h = pool.h; g.wpr = pool.w / 32; g.items = g.h * g.wpr;
+    const BigGeo g = big_geo(pool.h, pool.w);
     BigSmem sm;
     sm.src = big_smem;
     sm.elig = big_smem + (size_t)BIG_SRC * g.items;
@@ -542,8 +591,7 @@ big_env_kernel(slb_pool pool, BigArgs a) {
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 big_import_kernel(const uint16_t *__restrict__ cells, uint32_t *planes, int h, int w, uint32_t *plane_bits) {
-    BigGeo g;
-    g.h = h; g.wpr = w / 32; g.items = h * g.wpr;
+    const BigGeo g = big_geo(h, w);
     const uint4 *src = reinterpret_cast<const uint4 *>(cells + (size_t)blockIdx.x * h * w);  // 64 B per item
     uint32_t *dst = planes + (size_t)blockIdx.x * 16 * g.items;
     uint32_t bits = 0;
@@ -567,8 +615,7 @@ big_import_kernel(const uint16_t *__restrict__ cells, uint32_t *planes, int h, i
 
 __global__ void __launch_bounds__(256)
 big_export_kernel(const uint32_t *__restrict__ planes, uint16_t *cells, int h, int w) {
-    BigGeo g;
-    g.h = h; g.wpr = w / 32; g.items = h * g.wpr;
+    const BigGeo g = big_geo(h, w);
     const uint32_t *src = planes + (size_t)blockIdx.x * 16 * g.items;
     uint4 *dst = reinterpret_cast<uint4 *>(cells + (size_t)blockIdx.x * h * w);
     for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
@@ -593,8 +640,7 @@ __device__ __forceinline__ uint32_t big_cell_value(const uint32_t *planes, const
 __global__ void __launch_bounds__(256)
 big_obs_kernel(slb_pool pool, const uint32_t *__restrict__ board, const uint32_t *__restrict__ goals,
                const slb_env_state *__restrict__ state, int vh, int vw, int remove_white, uint16_t *obs) {
-    BigGeo g;
-    g.h = pool.h; g.wpr = pool.w / 32; g.items = g.h * g.wpr;
+    const BigGeo g = big_geo(pool.h, pool.w);
     const int i = blockIdx.x, h = pool.h, w = pool.w;
     const uint32_t *b = board + (size_t)i * 16 * g.items, *gl = goals + (size_t)i * 16 * g.items;
     const int x0 = state[i].agent_x, y0 = state[i].agent_y, level = state[i].level_id;
@@ -613,7 +659,7 @@ big_obs_kernel(slb_pool pool, const uint32_t *__restrict__ board, const uint32_t
         for (int it = 0; it < g.items; it++) {
             uint32_t m = em[it];
             while (m) {
-                const int y = it / g.wpr, x = (it - y * g.wpr) * 32 + __ffs(m) - 1;
+                const int y = it / g.wpr, x = (it - y * g.wpr) * 32 + __ffs(m) - 1;  // (rare) exit cells only
                 m &= m - 1;
                 int jy = pymod_w(y - y0 + h / 2, h) - h / 2;
                 int jx = pymod_w(x - x0 + w / 2, w) - w / 2;
