@@ -217,6 +217,12 @@ int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_
                 const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
                 uint16_t *d_obs, void *stream);
 
+/* ---- "next" row 2: SimpleSideEffectPenalty.step's count (env_wrappers.py:319-346) ------------------
+ * d_count[i] = number of cells of env i that differ from the level's initial board, ignoring the
+ * player's attribute bits, exit cells, red life that went away and non-red life on blue goals. */
+int slb_side_effect_penalty(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
+                            const slb_env_state *d_state, int32_t *d_count, void *stream);
+
 /* The channel split of safelife_env.py:152-154 for M packed words: d_out [M, n_channels] uint16,
  * d_out[m, c] = (d_words[m] >> d_channels[c]) & 1.  n_channels <= 16; d_out 4-byte aligned. */
 int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *d_channels, int n_channels,

@@ -332,3 +332,19 @@ def get_obs(board, goals, agent_loc, board0, view_shape=(15, 15), remove_white_g
         shift = np.array(list(output_channels), dtype=np.uint16)
         view = (view[..., None] & (np.uint16(1) << shift)) >> shift
     return view
+
+
+def side_effect_penalty_count(board, board0, goals):
+    """SimpleSideEffectPenalty.step's `side_effect` (env_wrappers.py:319-346) for one env, numpy."""
+    player = np.uint16(2 | 8 | 16 | 32 | 64)                                # CellTypes.player
+    b = np.asarray(board, dtype=np.uint16) & ~player                        # :326
+    s = np.asarray(board0, dtype=np.uint16) & ~player                       # :327
+    ex = (np.asarray(board0, dtype=np.uint16) & np.uint16(256)) != 0        # exit_locs
+    b = np.where(ex, s, b)                                                  # :329-330
+    red_life = np.uint16(1 | 512)
+    start_red = (s & red_life) == red_life                                  # :335
+    end_red = (b & red_life) == red_life
+    goal_cell = (np.asarray(goals, dtype=np.uint16) & np.uint16(7 << 9)) == np.uint16(1 << 11)
+    end_alive = (b & red_life) == np.uint16(1)
+    non_effects = (b == s) | (start_red & ~end_red) | (goal_cell & end_alive)   # :340
+    return int(np.sum(~non_effects))

@@ -586,6 +586,26 @@ int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_
     return SLB_OK;
 }
 
+int slb_side_effect_penalty(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
+                            const slb_env_state *d_state, int32_t *d_count, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || !d_board || !d_goals || !d_state || !d_count)
+        return fail(SLB_ERR_INVALID, "slb_side_effect_penalty: bad arguments");
+    if (n == 0) return SLB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (fast_shape(pool->h, pool->w))
+        res_penalty_kernel<<<RES_GRID(n), st>>>(*pool, n, (const uint32_t *)d_board, (const uint32_t *)d_goals,
+                                               d_state, d_count);
+    else if (big_shape(pool->h, pool->w))
+        big_penalty_kernel<<<n, 256, 0, st>>>(*pool, (const uint32_t *)d_board, (const uint32_t *)d_goals,
+                                             d_state, d_count);
+    else
+        penalty_generic_kernel<<<n, GEN_THREADS, 0, st>>>(*pool, (const uint16_t *)d_board,
+                                                         (const uint16_t *)d_goals, d_state, d_count);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
 int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *d_channels, int n_channels,
                      uint16_t *d_out, void *stream) {
     if (!d_words || !d_channels || !d_out || n_channels < 1 || n_channels > 16)

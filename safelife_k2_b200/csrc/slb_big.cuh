@@ -586,6 +586,27 @@ big_env_kernel(slb_pool pool, BigArgs a) {
         big_reset(pool, (level + a.auto_reset_stride) % pool.n_levels, g, gb, gg, board, goals, st, scratch);
 }
 
+// SimpleSideEffectPenalty's count of side-effect cells per env (env_wrappers.py:319-346); grid = N
+__global__ void __launch_bounds__(256)
+big_penalty_kernel(slb_pool pool, const uint32_t *__restrict__ board, const uint32_t *__restrict__ goals,
+                   const slb_env_state *__restrict__ state, int32_t *count) {
+    __shared__ int scratch[96];
+    const BigGeo g = big_geo(pool.h, pool.w);
+    const int i = blockIdx.x, level = state[i].level_id;
+    const size_t words = (size_t)16 * g.items;
+    const uint32_t *e0 = pool.exit_mask + (size_t)level * g.items;
+    int c = 0, d1 = 0, d2 = 0;
+    for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
+        uint32_t B[16], S[16], G[16];
+        big_load(board + i * words, g, it, pool.plane_groups[0], B);
+        big_load((const uint32_t *)pool.board_res + level * words, g, it, 15u, S);
+        big_load(goals + i * words, g, it, 3u, G);
+        c += __popc(side_effect_word(B, S, G, e0[it], 0xffffffffu));
+    }
+    big_sum3(c, d1, d2, scratch);
+    if (threadIdx.x == 0) count[i] = c;
+}
+
 // ---------------------------------------------------------------------------------------------
 // cells <-> resident planes for big boards (API boundary); grid = N, one item per thread per pass.
 // ---------------------------------------------------------------------------------------------

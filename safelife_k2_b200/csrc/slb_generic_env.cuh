@@ -2,6 +2,7 @@
 // kernels.  One CTA per env / episode.
 #pragma once
 #include "slb_generic_kernels.cuh"
+#include "slb_planes_env.cuh"
 
 namespace slb {
 
@@ -190,6 +191,21 @@ side_effect_generic_kernel(const uint16_t *__restrict__ board0, const uint16_t *
         for (int k = 0; k < kmax; k++) nk += sh_keys[k] != 0;
         nkeys[i] = sh_overflow ? -1 : nk;
     }
+}
+
+// SimpleSideEffectPenalty's count of side-effect cells per env (env_wrappers.py:319-346); grid = N
+__global__ void __launch_bounds__(GEN_THREADS)
+penalty_generic_kernel(slb_pool pool, const uint16_t *__restrict__ board,
+                       const uint16_t *__restrict__ goals, const slb_env_state *__restrict__ state,
+                       int32_t *count) {
+    __shared__ int scratch[96];
+    const int i = blockIdx.x, cells = pool.h * pool.w, level = state[i].level_id;
+    const uint16_t *b = board + (size_t)i * cells, *g = goals + (size_t)i * cells;
+    const uint16_t *s = pool.board + (size_t)level * cells;
+    int c = 0, d1 = 0, d2 = 0;
+    for (int k = threadIdx.x; k < cells; k += blockDim.x) c += side_effect_cell(b[k], s[k], g[k], (s[k] & EXIT) != 0);
+    block_sum3(c, d1, d2, scratch);
+    if (threadIdx.x == 0) count[i] = c;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -174,4 +174,39 @@ __device__ __forceinline__ void paint_exits(uint32_t P[16], uint32_t e0, int can
     if (can_exit) P[9] |= e0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// SimpleSideEffectPenalty's per-step count (env_wrappers.py:319-346) for one word of cells:
+// B = current board, S = the level's initial board, G = goals, e0 = initial exit cells.  The player
+// bits (agent, destructible, frozen, preserving, inhibiting = 122) are ignored on both boards, exit
+// cells count as unchanged, and a cell is no side effect if it is unchanged, or was red life and no
+// longer is, or lies on a blue goal and now holds non-red life.  Returns the mask of side-effect cells.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t side_effect_word(const uint32_t B[16], const uint32_t S[16],
+                                                     const uint32_t G[16], uint32_t e0, uint32_t wmask) {
+    uint32_t diff = 0;
+#pragma unroll
+    for (int b = 0; b < 16; b++) {
+        if (b == 1 || b == 3 || b == 4 || b == 5 || b == 6) continue;  // CellTypes.player
+        diff |= B[b] ^ S[b];
+    }
+    diff &= ~e0;                                   // board[exit_locs] = start_board[exit_locs]
+    const uint32_t b0 = (B[0] & ~e0) | (S[0] & e0), b9 = (B[9] & ~e0) | (S[9] & e0);
+    const uint32_t start_red = S[0] & S[9], end_red = b0 & b9;
+    const uint32_t goal_cell = G[11] & ~G[9] & ~G[10];
+    const uint32_t end_alive = b0 & ~b9;
+    const uint32_t non_effects = ~diff | (start_red & ~end_red) | (goal_cell & end_alive);
+    return ~non_effects & wmask;
+}
+
+// the same for one uint16 cell
+__device__ __forceinline__ int side_effect_cell(uint32_t b, uint32_t s, uint32_t g, bool is_exit) {
+    const uint32_t player = AGENT | DESTRUCTIBLE | FROZEN | PRESERVING | INHIBITING;
+    b &= ~player; s &= ~player;
+    if (is_exit) b = s;
+    const uint32_t red_life = ALIVE | RED;
+    const bool start_red = (s & red_life) == red_life, end_red = (b & red_life) == red_life;
+    const bool goal_cell = (g & COLORS) == BLUE, end_alive = (b & red_life) == ALIVE;
+    return !((b == s) || (start_red && !end_red) || (goal_cell && end_alive));
+}
+
 }  // namespace slb

@@ -336,6 +336,26 @@ res_score_kernel(slb_pool pool, int n, uint32_t *board, const uint32_t *goals, s
     }
 }
 
+// SimpleSideEffectPenalty's count of side-effect cells per env (env_wrappers.py:319-346)
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_penalty_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
+                   const uint32_t *__restrict__ goals, const slb_env_state *__restrict__ state,
+                   int32_t *count) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const size_t words = resident_words(g.h);
+    const int level = state[i].level_id;
+    uint32_t B[16], S[16], G[16];
+    load_res(board + i * words, g, pool.plane_groups[0], B);
+    load_res((const uint32_t *)pool.board_res + level * words, g, 15u, S);
+    load_res(goals + i * words, g, 3u, G);
+    const uint32_t e0 = g.row ? pool.exit_mask[(size_t)level * g.h + lane] : 0u;
+    const int c = warp_sum(__popc(side_effect_word(B, S, G, e0, g.row ? g.wmask : 0u)));
+    if (lane == 0) count[i] = c;
+}
+
 // ---------------------------------------------------------------------------------------------
 // cells <-> resident planes (API boundary).  The import ORs every cell it sees into *plane_bits.
 // ---------------------------------------------------------------------------------------------

@@ -14,6 +14,7 @@ Outputs (all np.savez_compressed):
     scenarios.npz     scripted execute_action cases on real SafeLifeGame objects (push/pull/exit/toggle)
     side_effects.npz  pre-EMD density counts of side_effect_score for finished episodes
     obs.npz           SafeLifeEnv.get_obs along short traces (several view shapes / channel sets)
+    wrappers.npz      rewards of MovementBonusWrapper / SimpleSideEffectPenalty around the real env
 """
 import hashlib
 import os
@@ -334,9 +335,49 @@ def make_obs():
     save("obs.npz", **out)
 
 
+# -------------------------------------------------------------------------------------------------
+def make_wrappers():
+    """Rewards of the reference's MovementBonusWrapper and SimpleSideEffectPenalty (env_wrappers.py)
+    around the real SafeLifeEnv, plus the penalty's side-effect count per step."""
+    rh._import()
+    from safelife import env_wrappers as ew
+    cases = [("prune-spawn", 3, 41, 42, 9), ("append-still", 5, 43, 44, 10), ("navigation", 6, 45, 46, 11)]
+    out = {"n_cases": np.int32(len(cases)), "penalty_coef": np.float64(0.7), "min_performance": np.float64(0.3)}
+    T = 160
+    for i, (archive, level, s, a, env_id) in enumerate(cases):
+        lv = rh.load_archive("benchmarks/v1.0/" + archive)
+        rng = np.random.RandomState(a)
+        actions = np.array([int(rng.randint(9)) for _ in range(T)], dtype=np.int32)
+        res = {}
+        for which in ("penalty", "movement"):
+            ctx = rh.fed_reference(s, env_id)
+            with ctx:
+                env = rh.make_env(levels=lv[level:level + 1], global_counter=None)
+                if which == "penalty":
+                    env = ew.SimpleSideEffectPenalty(env, penalty_coef=0.7, min_performance=0.3)
+                else:
+                    env = ew.MovementBonusWrapper(env)
+                env.reset()
+                ctx.rewind(0)
+                rew, side = [], []
+                for act in actions:
+                    o, r, done, info = env.step(int(act))
+                    rew.append(float(r))
+                    if which == "penalty":
+                        side.append(int(env.last_side_effect))
+                res[which] = (np.array(rew, np.float64), np.array(side, np.int64))
+        out.update({"archive_%d" % i: np.array(archive), "level_%d" % i: np.int32(level), "seed_%d" % i: np.uint64(s),
+                    "env_%d" % i: np.uint64(env_id), "actions_%d" % i: actions,
+                    "penalty_reward_%d" % i: res["penalty"][0], "side_effect_%d" % i: res["penalty"][1],
+                    "movement_reward_%d" % i: res["movement"][0]})
+        print("  wrappers %s: final side effect %d, sum rewards %.3f / %.3f" % (
+            archive, res["penalty"][1][-1], res["penalty"][0].sum(), res["movement"][0].sum()))
+    save("wrappers.npz", **out)
+
+
 if __name__ == "__main__":
     assert rh.available(), "needs /root/reference and `make -C oracle ref`"
-    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs"]
+    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs", "wrappers"]
     if "levels" in which:
         make_levels()
     if "kat" in which:
@@ -349,3 +390,5 @@ if __name__ == "__main__":
         make_side_effects()
     if "obs" in which:
         make_obs()
+    if "wrappers" in which:
+        make_wrappers()

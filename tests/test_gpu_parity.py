@@ -377,3 +377,77 @@ def test_resident_import_export_roundtrip(sl):
             b[i], c = slo.advance_board(b[i], 0.3, seed=2, env=i, counter=int(ctr[i]))
             ctr[i] = c
         assert (g.board.cpu().numpy() == b).all(), t
+
+
+def test_wrappers_golden(sl):
+    """MovementBonusWrapper / SimpleSideEffectPenalty (safelife_k2_b200/env_wrappers.py) against the
+    reference's wrappers around its real env (tests/golden/wrappers.npz)."""
+    from safelife_k2_b200 import env_wrappers as ew
+
+    d = gu.load("wrappers.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        for which in ("penalty", "movement"):
+            pool = sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 1))
+            env = sl.env.SafeLifeEnv(pool, num_envs=1, env_id0=int(d["env_%d" % i]), global_counter=None,
+                                     compute_obs=False)
+            env.seed(int(d["seed_%d" % i]))
+            if which == "penalty":
+                env = ew.SimpleSideEffectPenalty(env, penalty_coef=float(d["penalty_coef"]),
+                                                 min_performance=float(d["min_performance"]))
+            else:
+                env = ew.MovementBonusWrapper(env)
+            env.reset()
+            for t, a in enumerate(d["actions_%d" % i]):
+                _, r, _, _ = env.step(np.array([a]))
+                assert r.dtype == torch.float64
+                assert abs(float(r[0]) - d["%s_reward_%d" % (which, i)][t]) < 1e-12, (which, i, t)
+                if which == "penalty":
+                    assert int(env.last_side_effect[0]) == d["side_effect_%d" % i][t], (i, t)
+
+
+@pytest.mark.parametrize("h,w", [(26, 26), (9, 31), (40, 33), (40, 64)])
+def test_side_effect_penalty_vs_oracle(sl, h, w):
+    from safelife_k2_b200 import env_wrappers as ew
+
+    rng = np.random.RandomState(h + 7 * w)
+    lv = _random_levels(rng, 12, h, w)
+    n = 48
+    pool = sl.game.LevelPool(lv)
+    env = ew.SimpleSideEffectPenalty(
+        sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False), penalty_coef=1.0)
+    env.seed(1)
+    env.reset()
+    lvl = np.arange(n) % 12
+    for t in range(12):
+        env.step(rng.randint(9, size=n))
+        b, g = env.game.board.cpu().numpy(), env.game.goals.cpu().numpy()
+        want = [slo.side_effect_penalty_count(b[i], lv["board"][lvl[i]], g[i]) for i in range(n)]
+        assert env.last_side_effect.cpu().tolist() == want, t
+
+
+def test_continuing_env(sl):
+    """ContinuingEnv (env_wrappers.py:289-303): finishing a level restarts that env, only the time
+    limit ends an episode."""
+    from safelife_k2_b200 import env_wrappers as ew
+
+    # the exit is right of the agent and open (min_performance < 0): MOVE RIGHT finishes the level
+    board = np.zeros((2, 6, 6), np.uint16)
+    board[:, 2, 2] = 122
+    board[:, 2, 3] = 272
+    lv = {"board": board, "goals": np.zeros_like(board), "agent_loc": np.array([[2, 2], [2, 2]]),
+          "orientation": np.array([1, 1]), "spawn_prob": np.array([0.3, 0.3]), "min_performance": np.array([-1.0, -1.0])}
+    env = ew.ContinuingEnv(sl.env.SafeLifeEnv(sl.game.LevelPool(lv), num_envs=2, global_counter=None,
+                                              compute_obs=False, time_limit=3))
+    env.seed(0)
+    env.reset()
+    _, r, done, info = env.step(np.array([2, 0]))       # env 0 exits, env 1 idles
+    assert r.tolist() == [1, 0] and done.tolist() == [False, False]
+    st = env.game.state_numpy()
+    assert st["game_over"].tolist() == [0, 0] and st["episode_length"].tolist() == [0, 1]  # env 0 restarted
+    for _ in range(2):
+        _, r, done, info = env.step(np.array([0, 0]))
+    assert done.tolist() == [False, False]
+    _, r, done, info = env.step(np.array([0, 0]))       # env 1 reaches step 4 > time_limit 3
+    assert done.tolist() == [False, True] and info["times_up"].tolist() == [False, True]

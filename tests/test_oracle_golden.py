@@ -157,3 +157,22 @@ def test_get_obs_golden():
                 assert (obs() == want[k]).all(), (i, t)
                 k += 1
         assert k == len(want)
+
+
+def test_side_effect_penalty_golden():
+    """numpy restatement of SimpleSideEffectPenalty's count along the reference traces (wrappers.npz)"""
+    d = gu.load("wrappers.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        one = gu.level_slice(lv, l0, l0 + 1)
+        one["min_performance"] = np.array([float(d["min_performance"])])  # the wrapper overrides it at reset
+        env = slo.OracleBatchEnv(slo.OraclePool(**one), [0], seed=int(d["seed_%d" % i]),
+                                 env_id0=int(d["env_%d" % i]))
+        last, coef = 0, float(d["penalty_coef"])
+        for t, a in enumerate(d["actions_%d" % i]):
+            r, _ = env.step([a])
+            side = slo.side_effect_penalty_count(env.boards[0], one["board"][0], env.goals[0])
+            assert side == d["side_effect_%d" % i][t], (i, t)
+            assert abs((float(r[0]) - (side - last) * coef) - d["penalty_reward_%d" % i][t]) < 1e-12, (i, t)
+            last = side
