@@ -10,4 +10,5 @@ points/performance, side-effect rollouts) behind the reference's own interfaces.
 All compute is CUDA (libsafelife_b200.so, sm_100a) through the C ABI in include/safelife_b200.h.
 There is no CPU fallback; importing the compute modules without the built library raises.
 """
-__all__ = ["speedups", "safelife_game", "safelife_env", "side_effects", "distributed"]
+__all__ = ["speedups", "safelife_game", "safelife_env", "side_effects", "env_wrappers", "benchmarking",
+           "distributed"]

@@ -96,6 +96,7 @@ class LevelPool(object):
         rec = _stack_levels(levels)
         self.device = _dev(device)
         self.host = rec
+        self.names = _level_names(levels)
         P, H, W = rec["board"].shape
         if H < 3 or W < 3:
             raise ValueError("boards must be at least 3x3 (got %dx%d)" % (H, W))
@@ -155,6 +156,18 @@ def _stack_levels(levels):
     if out["board"].ndim != 3 or out["board"].shape != out["goals"].shape:
         raise ValueError("levels must stack to board/goals of shape [P,H,W]")
     return out
+
+
+def _level_names(levels):
+    """Level titles when the records carry them (the `name` field of reference archives)."""
+    try:
+        if isinstance(levels, np.ndarray) and levels.dtype.fields and "name" in levels.dtype.fields:
+            return [n.decode() if isinstance(n, bytes) else str(n) for n in levels["name"]]
+        if isinstance(levels, dict) and "name" in levels:
+            return [str(n) for n in levels["name"]]
+    except Exception:
+        pass
+    return None
 
 
 def load_levels(path):

@@ -15,6 +15,7 @@ Outputs (all np.savez_compressed):
     side_effects.npz  pre-EMD density counts of side_effect_score for finished episodes
     obs.npz           SafeLifeEnv.get_obs along short traces (several view shapes / channel sets)
     wrappers.npz      rewards of MovementBonusWrapper / SimpleSideEffectPenalty around the real env
+    benchmark_log.npz the YAML episode records RecordingSafeLifeWrapper writes (EMD stubbed to 0)
 """
 import hashlib
 import os
@@ -375,9 +376,46 @@ def make_wrappers():
     save("wrappers.npz", **out)
 
 
+# -------------------------------------------------------------------------------------------------
+def make_benchmark_log():
+    """The YAML episode record RecordingSafeLifeWrapper.log_episode writes (env_wrappers.py:172-231)
+    for short episodes of the real env (EMD stubbed to 0, pyemd being absent)."""
+    import io
+    rh._import()
+    from safelife import env_wrappers as ew, side_effects
+    cases = [("prune-spawn", 2, 51, 52, 20, 35), ("append-still", 8, 53, 54, 21, 25)]
+    out = {"n_cases": np.int32(len(cases))}
+    orig = side_effects.earth_mover_distance
+    side_effects.earth_mover_distance = lambda a, b, *args, **kw: 0.0
+    try:
+        for i, (archive, level, s, a, env_id, tl) in enumerate(cases):
+            lv = rh.load_archive("benchmarks/v1.0/" + archive)
+            rng = np.random.RandomState(a)
+            actions = np.array([int(rng.randint(9)) for _ in range(tl + 1)], dtype=np.int32)
+            ctx = rh.fed_reference(s, env_id)
+            log = io.StringIO()
+            with ctx:
+                env = rh.make_env(levels=lv[level:level + 1], global_counter=None, time_limit=tl)
+                env = ew.RecordingSafeLifeWrapper(env, log_file=log, video_name=None)
+                env.reset()
+                ctx.rewind(0)
+                for act in actions:
+                    o, r, done, info = env.step(int(act))
+                assert done
+                title = env.game.title
+            out.update({"archive_%d" % i: np.array(archive), "level_%d" % i: np.int32(level),
+                        "seed_%d" % i: np.uint64(s), "env_%d" % i: np.uint64(env_id), "actions_%d" % i: actions,
+                        "time_limit_%d" % i: np.int32(tl), "title_%d" % i: np.array(str(title)),
+                        "log_%d" % i: np.array(log.getvalue())})
+            print(log.getvalue())
+    finally:
+        side_effects.earth_mover_distance = orig
+    save("benchmark_log.npz", **out)
+
+
 if __name__ == "__main__":
     assert rh.available(), "needs /root/reference and `make -C oracle ref`"
-    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs", "wrappers"]
+    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs", "wrappers", "log"]
     if "levels" in which:
         make_levels()
     if "kat" in which:
@@ -392,3 +430,5 @@ if __name__ == "__main__":
         make_obs()
     if "wrappers" in which:
         make_wrappers()
+    if "log" in which:
+        make_benchmark_log()

@@ -451,3 +451,31 @@ def test_continuing_env(sl):
     assert done.tolist() == [False, False]
     _, r, done, info = env.step(np.array([0, 0]))       # env 1 reaches step 4 > time_limit 3
     assert done.tolist() == [False, True] and info["times_up"].tolist() == [False, True]
+
+
+def test_benchmark_log_golden(sl, tmp_path):
+    """benchmarking.run_benchmark writes the reference's YAML episode record (env_wrappers.py:195-221):
+    same header text and the same parsed content as RecordingSafeLifeWrapper's log for the same episode."""
+    import yaml
+    from safelife_k2_b200 import benchmarking as bm
+
+    d = gu.load("benchmark_log.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        acts = iter(d["actions_%d" % i])
+        log = str(tmp_path / ("bench_%d.yaml" % i))
+        eps = bm.run_benchmark(gu.level_slice(lv, l0, l0 + 1), lambda obs: torch.tensor([next(acts)]), log,
+                               names=[str(d["title_%d" % i])], time_limit=int(d["time_limit_%d" % i]),
+                               seed=int(d["seed_%d" % i]), env_id0=int(d["env_%d" % i]), emd=False)
+        assert len(eps) == 1
+        text = open(log).read()
+        assert text.startswith("# SafeLife benchmark data\n---\n")
+        want_txt = str(d["log_%d" % i])
+        ours, want = yaml.safe_load(text)[0], yaml.safe_load(want_txt)[0]
+        ours.pop("episode"); want.pop("episode")
+        assert ours == want, (ours, want)
+        head = lambda t: t.split("  side effects:")[0].replace("episode: 1", "episode: -1")  # noqa: E731
+        assert head(text.split("---\n", 1)[1]) == head(want_txt)
+        stats = bm.load_benchmarks(log)
+        assert stats["length"].tolist() == [want["length"]] and set(stats["side effects"]) == set(want["side effects"])
