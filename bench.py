@@ -231,7 +231,7 @@ def run_b200(args):
     # flight on two streams (the double-buffered actor loop: while one batch's results travel back, the
     # next batch steps); each step's outputs are waited for before that batch's buffers are reused.
     e2e_steps = min(K, 1000)
-    depth = 2
+    depth = 3
     h_act = torch.from_numpy(rng.randint(9, size=(n_act, n)).astype(np.uint8)).pin_memory()
     h_out = [torch.zeros(5 * n, dtype=torch.uint8).pin_memory() for _ in range(depth)]
     streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]
@@ -248,9 +248,14 @@ def run_b200(args):
         for s in range(depth):
             envs[0].wait(streams[s])
 
-    e2e_loop(2 * depth + 2)
+    e2e_loop(2 * ring + depth)  # every batch's stepper (staging block + step graph) exists before the timed loop
     if world > 1:
         torch.distributed.barrier()
+    if os.environ.get("SLB_BENCH_DEBUG"):
+        for _ in range(6):
+            t0 = time.perf_counter()
+            e2e_loop(200)
+            print("e2e chunk of 200: %.1f us/step" % ((time.perf_counter() - t0) / 200 * 1e6), file=sys.stderr)
     t0 = time.perf_counter()
     e2e_loop(e2e_steps)
     e2e_s = distributed.max_over_ranks(time.perf_counter() - t0, dev)
@@ -285,7 +290,7 @@ def run_b200(args):
         "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "env-steps/s", "h2d_bytes_per_step": n,
                 "d2h_bytes_per_step": 5 * n, "steps": e2e_steps,
                 "what": "SafeLifeEnv.step_host -> slb_env_step_host_async: per step pinned uint8 actions H2D, fused step, "
-                        "int32 reward + uint8 done D2H to pinned memory; 2 independent batches in flight on 2 streams",
+                        "int32 reward + uint8 done D2H to pinned memory; 3 independent batches in flight on 3 streams",
                 "serial_value": n * world / e2e_serial_s,
                 "serial_what": "one step at a time: copy in, step, copy out, wait"},
         "stats_allreduce": distributed.stats_dict(stats),

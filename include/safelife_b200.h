@@ -184,14 +184,30 @@ int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       int auto_reset_stride, void *stream);
 
 /* The same without the final wait: H2D copy, step and D2H copy are queued on `stream` (give steps that
- * should overlap their own streams; at most 8 streams per calling thread); the host buffers must be
- * page-locked for the copies to be asynchronous and are valid after slb_stream_wait(stream). */
+ * should overlap their own streams; at most 8 streams per calling thread).  h_actions is consumed
+ * before the call returns; h_reward / h_done are valid only after slb_stream_wait(stream), called from
+ * the SAME host thread, returns (a plain cudaStreamSynchronize is not enough: on a non-default stream
+ * the three operations run as one cached CUDA graph through a page-locked staging block inside the
+ * library and slb_stream_wait hands the results over; the host buffers need not be page-locked). */
 int slb_env_step_host_async(const slb_pool *pool, int n, void *d_board, void *d_goals,
                             slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
                             uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                             int auto_reset_stride, void *stream);
-/* Low-latency wait for everything queued on `stream` (spins on cudaStreamQuery). */
+/* Low-latency wait for everything queued on `stream` (spins on cudaStreamQuery), then delivers the
+ * outputs of the slb_env_step_host_async call in flight on it, if any. */
 int slb_stream_wait(void *stream);
+
+/* A host stepper binds every argument of slb_env_step_host_async that does not change from step to
+ * step, so that the per-step call crosses the FFI with 4 arguments (a ctypes call costs ~0.25 us per
+ * argument).  `pool` must outlive the stepper.  step = slb_env_step_host_async, wait =
+ * slb_stream_wait on the bound stream (same thread rule). */
+typedef struct slb_stepper slb_stepper;
+int slb_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                       int time_limit, uint64_t seed, uint64_t env_id0, int auto_reset_stride,
+                       void *stream, slb_stepper **out);
+int slb_stepper_step(slb_stepper *s, const uint8_t *h_actions, int32_t *h_reward, uint8_t *h_done);
+int slb_stepper_wait(slb_stepper *s);
+void slb_stepper_destroy(slb_stepper *s);
 
 /* ---- A13/A14: side_effect_score up to the EMD (side_effects.py:59-141) ---------------------------
  * For episode i: b0 = d_board0[i] advanced d_num_steps[i] times, then num_samples paired steps of

@@ -59,6 +59,10 @@ SYMBOLS = {
     "slb_env_step_host": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _vp]),
     "slb_env_step_host_async": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _vp]),
     "slb_stream_wait": (_i, [_vp]),
+    "slb_stepper_create": (_i, [_PP, _i, _vp, _vp, _vp, _i, _u64, _u64, _i, _vp, C.POINTER(_vp)]),
+    "slb_stepper_step": (_i, [_vp, _vp, _vp, _vp]),
+    "slb_stepper_wait": (_i, [_vp]),
+    "slb_stepper_destroy": (None, [_vp]),
     "slb_side_effect_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _vp, _u64, _u64, _vp, _i, _vp,
                                     _vp, _vp, _vp, _vp]),
     "slb_accumulate_stats": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),

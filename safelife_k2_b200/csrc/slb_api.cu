@@ -446,28 +446,187 @@ int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
 }
 
 
-// One device staging block per (calling thread, stream), grown on demand:
-// [reward 4n | done n | pad | actions n].  Steps in flight on different streams never share one.
+// ---- host-buffer steps ---------------------------------------------------------------------------
+// One slot per (calling thread, stream): a device staging block [reward 4n | done n | pad | actions n]
+// and a pinned host mirror of it.  A step runs as ONE instantiated CUDA graph {H2D actions, fused step,
+// D2H reward+done} between those blocks, so that it costs the host one cudaGraphLaunch instead of two
+// copies and a kernel launch; the caller's buffers are filled from the pinned mirror by
+// slb_stream_wait (they need not be page-locked).  A slb_stepper owns its graph; the free function
+// slb_env_step_host_async keeps a small least-recently-used cache of graphs per slot, keyed by the
+// whole argument set.  SLB_HOST_GRAPH=0, the legacy default stream or a stream that is being captured
+// take the plain path: copies straight from / to the caller's buffers.
 namespace {
-struct HostIo { cudaStream_t st; uint8_t *d; size_t cap; };
-int host_io_block(cudaStream_t st, size_t need, uint8_t **out) {
-    thread_local HostIo slots[8] = {};
-    thread_local int used = 0;
-    HostIo *s = nullptr;
-    for (int k = 0; k < used; k++)
-        if (slots[k].st == st) s = &slots[k];
+struct StepKey {
+    slb_pool pool;
+    int n, time_limit, stride, pad;
+    void *board, *goals, *state;
+    uint64_t seed, env_id0;
+};
+struct StepGraph {
+    StepKey key;
+    cudaGraphExec_t exec;
+    uint64_t stamp;  // last use (LRU)
+    uint8_t *d, *h;  // the staging blocks the graph copies between (a slot's, see below)
+};
+constexpr int kGraphsPerSlot = 32;
+struct HostIo {
+    cudaStream_t st;
+    uint8_t *d, *h;
+    size_t cap;
+    StepGraph graphs[kGraphsPerSlot];
+    int n_graphs;
+    uint64_t clock;
+    int32_t *pend_reward;  // outputs of the step in flight still to be copied out of `h`
+    uint8_t *pend_done;
+    int pend_n;
+};
+thread_local HostIo g_slots[8] = {};
+thread_local int g_slots_used = 0;
+
+HostIo *find_slot(cudaStream_t st) {
+    for (int k = 0; k < g_slots_used; k++)
+        if (g_slots[k].st == st) return &g_slots[k];
+    return nullptr;
+}
+
+int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
+    HostIo *s = find_slot(st);
     if (!s) {
-        if (used == 8) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 8 streams per thread");
-        s = &slots[used++];
-        s->st = st; s->d = nullptr; s->cap = 0;
+        if (g_slots_used == 8) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 8 streams per thread");
+        s = &g_slots[g_slots_used++];
+        memset(s, 0, sizeof(*s));
+        s->st = st;
     }
     if (need > s->cap) {
+        SLB_CUDA(cudaStreamSynchronize(st));
+        for (int k = 0; k < s->n_graphs; k++) cudaGraphExecDestroy(s->graphs[k].exec);
+        s->n_graphs = 0;  // (graphs owned by steppers notice the new blocks and rebuild)
         if (s->d) cudaFree(s->d);
-        s->d = nullptr; s->cap = 0;
+        if (s->h) cudaFreeHost(s->h);
+        s->d = s->h = nullptr; s->cap = 0;
         SLB_CUDA(cudaMalloc(&s->d, need));
+        SLB_CUDA(cudaMallocHost(&s->h, need));
         s->cap = need;
     }
-    *out = s->d;
+    *out = s;
+    return SLB_OK;
+}
+
+int finish_pending(HostIo *s) {
+    cudaError_t q;  // spin on the stream instead of a blocking wait: a step takes a few microseconds
+    while ((q = cudaStreamQuery(s->st)) == cudaErrorNotReady) {}
+    if (q != cudaSuccess) return fail(SLB_ERR_CUDA, "stream wait: %s", cudaGetErrorString(q));
+    if (s->pend_n) {
+        if (s->pend_reward) memcpy(s->pend_reward, s->h, (size_t)4 * s->pend_n);
+        if (s->pend_done) memcpy(s->pend_done, s->h + (size_t)4 * s->pend_n, (size_t)s->pend_n);
+        s->pend_n = 0;
+    }
+    return SLB_OK;
+}
+
+bool host_graphs_enabled() {
+    static const bool on = []() { const char *v = getenv("SLB_HOST_GRAPH"); return !v || v[0] != '0'; }();
+    return on;
+}
+
+inline size_t io_off_act(int n) { return ((size_t)5 * n + 15) & ~(size_t)15; }
+
+// capture {H2D actions, step, D2H reward+done} on the slot's stream and instantiate it
+int build_step_graph(HostIo *s, const StepKey &k, cudaGraphExec_t *exec) {
+    const size_t off_done = (size_t)4 * k.n, off_act = io_off_act(k.n);
+    cudaGraph_t graph = nullptr;
+    SLB_CUDA(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
+    cudaError_t e1 = cudaMemcpyAsync(s->d + off_act, s->h + off_act, (size_t)k.n, cudaMemcpyHostToDevice, s->st);
+    int rc = slb_env_step(&k.pool, k.n, k.board, k.goals, (slb_env_state *)k.state, s->d + off_act, k.time_limit,
+                          k.seed, k.env_id0, (int32_t *)s->d, s->d + off_done, k.stride, (void *)s->st);
+    cudaError_t e2 = cudaMemcpyAsync(s->h, s->d, (size_t)5 * k.n, cudaMemcpyDeviceToHost, s->st);
+    cudaError_t e3 = cudaStreamEndCapture(s->st, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    g_launches.fetch_sub(1, std::memory_order_relaxed);  // captured, not launched
+    if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        return fail(SLB_ERR_CUDA, "slb_env_step_host: graph capture failed");
+    }
+    cudaError_t e4 = cudaGraphInstantiate(exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e4 != cudaSuccess) return fail(SLB_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e4));
+    static const bool dbg = getenv("SLB_DEBUG") != nullptr;
+    if (dbg) fprintf(stderr, "[slb] step graph built: stream %p, n=%d\n", (void *)s->st, k.n);
+    return SLB_OK;
+}
+
+// `own`: the caller's graph (a stepper's), or NULL to use the slot's cache
+int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+              const uint8_t *h_actions, int time_limit, uint64_t seed, uint64_t env_id0, int32_t *h_reward,
+              uint8_t *h_done, int auto_reset_stride, void *stream, StepGraph *own) {
+    if (n < 0 || !h_actions) return fail(SLB_ERR_INVALID, "slb_env_step_host: bad arguments");
+    if (n == 0) return SLB_OK;
+    if (int rc = check_pool(pool)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t off_done = (size_t)4 * n, off_act = io_off_act(n);
+    HostIo *s = nullptr;
+    if (int rc = host_io_slot(st, off_act + (size_t)n, &s)) return rc;
+    if (s->pend_n)  // an earlier step on this stream was never waited for: deliver its outputs first
+        if (int rc = finish_pending(s)) return rc;
+    uint8_t *d_io = s->d;
+
+    bool graphed = host_graphs_enabled() && st != nullptr && st != cudaStreamLegacy && st != cudaStreamPerThread;
+    if (graphed) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        SLB_CUDA(cudaStreamIsCapturing(st, &cs));
+        graphed = cs == cudaStreamCaptureStatusNone;
+    }
+    if (!graphed) {
+        SLB_CUDA(cudaMemcpyAsync(d_io + off_act, h_actions, (size_t)n, cudaMemcpyHostToDevice, st));
+        int rc = slb_env_step(pool, n, d_board, d_goals, d_state, d_io + off_act, time_limit, seed, env_id0,
+                              (int32_t *)d_io, d_io + off_done, auto_reset_stride, stream);
+        if (rc) return rc;
+        if (h_reward && h_done == (uint8_t *)(h_reward + n)) {  // adjacent host outputs: one copy
+            SLB_CUDA(cudaMemcpyAsync(h_reward, d_io, (size_t)5 * n, cudaMemcpyDeviceToHost, st));
+        } else {
+            if (h_done) SLB_CUDA(cudaMemcpyAsync(h_done, d_io + off_done, (size_t)n, cudaMemcpyDeviceToHost, st));
+            if (h_reward) SLB_CUDA(cudaMemcpyAsync(h_reward, d_io, (size_t)4 * n, cudaMemcpyDeviceToHost, st));
+        }
+        return SLB_OK;
+    }
+
+    StepKey key;
+    memset(&key, 0, sizeof(key));
+    key.pool = *pool; key.n = n; key.time_limit = time_limit; key.stride = auto_reset_stride;
+    key.board = d_board; key.goals = d_goals; key.state = d_state; key.seed = seed; key.env_id0 = env_id0;
+    StepGraph *hit = nullptr;
+    if (own) {
+        if (own->exec && own->d == s->d && own->h == s->h && !memcmp(&own->key, &key, sizeof(key))) {
+            hit = own;
+        } else {
+            if (own->exec) { cudaGraphExecDestroy(own->exec); own->exec = nullptr; }
+            if (int rc = build_step_graph(s, key, &own->exec)) { own->exec = nullptr; return rc; }
+            own->key = key; own->d = s->d; own->h = s->h;
+            hit = own;
+        }
+    } else {
+        for (int k = 0; k < s->n_graphs; k++)
+            if (!memcmp(&s->graphs[k].key, &key, sizeof(key))) { hit = &s->graphs[k]; break; }
+        if (!hit) {
+            cudaGraphExec_t exec = nullptr;
+            if (int rc = build_step_graph(s, key, &exec)) return rc;
+            if (s->n_graphs < kGraphsPerSlot) {
+                hit = &s->graphs[s->n_graphs++];
+            } else {  // replace the least recently used one
+                hit = &s->graphs[0];
+                for (int k = 1; k < kGraphsPerSlot; k++)
+                    if (s->graphs[k].stamp < hit->stamp) hit = &s->graphs[k];
+                cudaGraphExecDestroy(hit->exec);
+            }
+            hit->exec = exec; hit->key = key; hit->d = s->d; hit->h = s->h;
+        }
+        hit->stamp = ++s->clock;
+    }
+    memcpy(s->h + off_act, h_actions, (size_t)n);
+    SLB_CUDA(cudaGraphLaunch(hit->exec, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);  // the step kernel inside the graph
+    s->pend_reward = h_reward; s->pend_done = h_done; s->pend_n = n;
     return SLB_OK;
 }
 }  // namespace
@@ -476,23 +635,8 @@ int slb_env_step_host_async(const slb_pool *pool, int n, void *d_board, void *d_
                             slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
                             uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                             int auto_reset_stride, void *stream) {
-    if (n < 0 || !h_actions) return fail(SLB_ERR_INVALID, "slb_env_step_host: bad arguments");
-    if (n == 0) return SLB_OK;
-    cudaStream_t st = (cudaStream_t)stream;
-    const size_t off_done = (size_t)4 * n, off_act = ((size_t)5 * n + 15) & ~(size_t)15;
-    uint8_t *d_io = nullptr;
-    if (int rc = host_io_block(st, off_act + (size_t)n, &d_io)) return rc;
-    SLB_CUDA(cudaMemcpyAsync(d_io + off_act, h_actions, (size_t)n, cudaMemcpyHostToDevice, st));
-    int rc = slb_env_step(pool, n, d_board, d_goals, d_state, d_io + off_act, time_limit, seed, env_id0,
-                          (int32_t *)d_io, d_io + off_done, auto_reset_stride, stream);
-    if (rc) return rc;
-    if (h_reward && h_done == (uint8_t *)(h_reward + n)) {  // adjacent host outputs: one copy
-        SLB_CUDA(cudaMemcpyAsync(h_reward, d_io, (size_t)5 * n, cudaMemcpyDeviceToHost, st));
-    } else {
-        if (h_done) SLB_CUDA(cudaMemcpyAsync(h_done, d_io + off_done, (size_t)n, cudaMemcpyDeviceToHost, st));
-        if (h_reward) SLB_CUDA(cudaMemcpyAsync(h_reward, d_io, (size_t)4 * n, cudaMemcpyDeviceToHost, st));
-    }
-    return SLB_OK;
+    return host_step(pool, n, d_board, d_goals, d_state, h_actions, time_limit, seed, env_id0, h_reward,
+                     h_done, auto_reset_stride, stream, nullptr);
 }
 
 int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
@@ -506,11 +650,51 @@ int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
 }
 
 int slb_stream_wait(void *stream) {
-    // spin on the stream instead of a blocking wait: a step takes a few microseconds
+    if (HostIo *s = find_slot((cudaStream_t)stream)) return finish_pending(s);
     cudaError_t q;
     while ((q = cudaStreamQuery((cudaStream_t)stream)) == cudaErrorNotReady) {}
     if (q != cudaSuccess) return fail(SLB_ERR_CUDA, "stream wait: %s", cudaGetErrorString(q));
     return SLB_OK;
+}
+
+struct slb_stepper {
+    const slb_pool *pool;
+    int n, time_limit, stride;
+    void *board, *goals;
+    slb_env_state *state;
+    uint64_t seed, env_id0;
+    void *stream;
+    StepGraph graph;
+};
+
+int slb_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                       int time_limit, uint64_t seed, uint64_t env_id0, int auto_reset_stride,
+                       void *stream, slb_stepper **out) {
+    if (int rc = check_pool(pool)) return rc;
+    if (!out || n < 0 || !d_board || !d_goals || !d_state)
+        return fail(SLB_ERR_INVALID, "slb_stepper_create: bad arguments");
+    slb_stepper *s = new slb_stepper{pool, n, time_limit, auto_reset_stride, d_board, d_goals, d_state,
+                                     seed, env_id0, stream, {}};
+    memset(&s->graph, 0, sizeof(s->graph));
+    *out = s;
+    return SLB_OK;
+}
+
+int slb_stepper_step(slb_stepper *s, const uint8_t *h_actions, int32_t *h_reward, uint8_t *h_done) {
+    if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
+    return host_step(s->pool, s->n, s->board, s->goals, s->state, h_actions, s->time_limit, s->seed,
+                     s->env_id0, h_reward, h_done, s->stride, s->stream, &s->graph);
+}
+
+int slb_stepper_wait(slb_stepper *s) {
+    if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
+    return slb_stream_wait(s->stream);
+}
+
+void slb_stepper_destroy(slb_stepper *s) {
+    if (!s) return;
+    if (s->graph.exec) cudaGraphExecDestroy(s->graph.exec);
+    delete s;
 }
 
 int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, int n, int h, int w,

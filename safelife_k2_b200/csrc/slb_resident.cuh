@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(RES_WARPS * 32, 7)
 res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                        const uint8_t *__restrict__ actions, int t_steps, int time_limit,
                        uint64_t seed, uint64_t env_id0, int32_t *reward_out, uint8_t *done_out,
-                       int auto_reset_stride) {
+                       int auto_reset_stride, int l2_prefetch) {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
     // Programmatic dependent launch: let the next kernel on the stream begin launching now (its CTAs
@@ -165,6 +165,17 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
     const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);  // resident words per board: 16 * H
     uint32_t *bp = board + off, *gp = goals + off;
     uint32_t B[16], G[16];
+    if (l2_prefetch) {
+        // While the previous kernel on the stream drains, pull this env's lines from HBM into L2
+        // (one 128-byte line per lane).  L2 is the point of coherence, so a line prefetched before
+        // the previous kernel's last writes land still reads back current after the wait below.
+        const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
+        const char *pf = nullptr;
+        if (lane < nb) pf = (const char *)bp + lane * 128;
+        else if (lane < nb + ng) pf = (const char *)gp + (lane - nb) * 128;
+        else if (lane == nb + ng) pf = (const char *)(state + i);
+        if (pf) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
     int action = actions[i];
@@ -214,6 +225,8 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     // launched with programmatic stream serialization (see the griddepcontrol pair in the kernel)
     static const bool pdl = []() { const char *v = getenv("SLB_PDL"); return !v || v[0] != '0'; }();
+    static const bool pf = []() { const char *v = getenv("SLB_L2_PREFETCH"); return !v || v[0] != '0'; }();
+    const int l2_prefetch = pdl && pf;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -226,7 +239,7 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
     cfg.numAttrs = pdl ? 1 : 0;
 #define SLB_ROLL2(GBV, GGV, HWV)                                                                     \
     cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV, HWV>, pool, n, board, goals, state,     \
-                       actions, t_steps, time_limit, seed, env0, reward, done, stride)
+                       actions, t_steps, time_limit, seed, env0, reward, done, stride, l2_prefetch)
 #define SLB_ROLL(GBV, GGV)                                                                           \
     do {                                                                                             \
         if (pool.h == 26 && pool.w == 26) SLB_ROLL2(GBV, GGV, 26);                                   \

@@ -74,6 +74,7 @@ class SafeLifeEnv(object):
         self.num_envs = int(self.num_envs)
         self._seed = 0
         self._lib = _lib.load()
+        self._steppers = {}
         self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
         dev = self.pool.device
         self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
@@ -173,16 +174,45 @@ class SafeLifeEnv(object):
         arrays.  sync=False only queues the copies and the step on `stream` (a torch stream; default the
         current one) — call wait(stream) before reading the outputs; independent env batches stepped on
         different streams overlap."""
+        st = (stream if stream is not None else torch.cuda.current_stream()).cuda_stream
         g = self.game
+        key = (st, id(g), self.time_limit, g.seed, self.auto_reset)
+        sp = self._steppers.get(key)
+        if sp is None:
+            sp = self._make_stepper(key, st)
         if torch.cuda.current_device() != self._dev_index:
             torch.cuda.set_device(self._dev_index)
-        st = (stream if stream is not None else torch.cuda.current_stream()).cuda_stream
-        fn = self._lib.slb_env_step_host if sync else self._lib.slb_env_step_host_async
-        rc = fn(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                _hptr(actions_host), self.time_limit, g.seed, g.env_id0, _hptr(reward_host),
-                _hptr(done_host), self._stride() if self.auto_reset else 0, st)
+        rc = self._lib.slb_stepper_step(sp, _hptr(actions_host), _hptr(reward_host), _hptr(done_host))
+        if rc == 0 and sync:
+            rc = self._lib.slb_stepper_wait(sp)
         if rc:
             _lib.check(rc)
+
+    def _make_stepper(self, key, st):
+        """Bind the per-env-batch arguments once (slb_stepper_create): the per-step FFI call then
+        carries only the three host pointers."""
+        import ctypes
+        g = self.game
+        if len(self._steppers) >= 64:
+            self._drop_steppers()
+        out = ctypes.c_void_p()
+        _lib.check(self._lib.slb_stepper_create(
+            self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+            int(self.time_limit), g.seed, g.env_id0, self._stride() if self.auto_reset else 0, st,
+            ctypes.byref(out)))
+        self._steppers[key] = out
+        return out
+
+    def _drop_steppers(self):
+        for sp in self._steppers.values():
+            self._lib.slb_stepper_destroy(sp)
+        self._steppers.clear()
+
+    def __del__(self):
+        try:
+            self._drop_steppers()
+        except Exception:
+            pass
 
     def wait(self, stream=None):
         st = (stream if stream is not None else torch.cuda.current_stream()).cuda_stream

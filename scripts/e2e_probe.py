@@ -1,4 +1,7 @@
-"""Where does a host-buffer step spend its time?  (GPU box)"""
+"""Where does a host-buffer step spend its time?  (GPU box)
+
+    python scripts/e2e_probe.py [n_envs]        # SLB_HOST_GRAPH=0/1 selects the path of step_host
+"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -8,42 +11,53 @@ from safelife_k2_b200.safelife_env import SafeLifeEnv
 from safelife_k2_b200.safelife_game import LevelPool
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+nb = int(sys.argv[2]) if len(sys.argv) > 2 else 14
 pool = LevelPool(gu.levels("append-still"))
-env = SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False, auto_reset=True)
-env.seed(0); env.reset()
-g = env.game
+envs = []
+for b in range(nb):
+    e = SafeLifeEnv(pool, num_envs=n, env_id0=b * n, global_counter=None, compute_obs=False, auto_reset=True)
+    e.seed(0); e.reset()
+    envs.append(e)
 lib = _lib.load()
-st = torch.cuda.current_stream().cuda_stream
-acts = torch.randint(0, 9, (n,), dtype=torch.uint8, device="cuda")
 h_act = torch.randint(0, 9, (n,), dtype=torch.uint8).pin_memory()
-h_out = torch.zeros(5 * n, dtype=torch.uint8).pin_memory()
-hr, hd = h_out.data_ptr(), h_out.data_ptr() + 4 * n
-args = (pool.c, n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr())
-tail = (1000, 0, 0)
+outs = [torch.zeros(5 * n, dtype=torch.uint8).pin_memory() for _ in range(4)]
+ap = h_act.data_ptr()
+op = [(o.data_ptr(), o.data_ptr() + 4 * n) for o in outs]
+pc = time.perf_counter
+ALL_STREAMS = [torch.cuda.Stream() for _ in range(4)]
 
-def bench(name, fn, iters=2000):
-    for _ in range(20): fn()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(iters): fn()
-    torch.cuda.synchronize()
-    print("%-40s %7.2f us/step" % (name, (time.perf_counter() - t0) / iters * 1e6))
 
-bench("device step, no sync (launch rate)", lambda: lib.slb_env_step(*args, acts.data_ptr(), *tail, env._reward.data_ptr(), env._done.data_ptr(), 100, st))
-def dsync():
-    lib.slb_env_step(*args, acts.data_ptr(), *tail, env._reward.data_ptr(), env._done.data_ptr(), 100, st)
-    torch.cuda.current_stream().synchronize()
-bench("device step + stream sync", dsync)
-for z in ("1", "0"):
-    os.environ["SLB_E2E_ZEROCOPY"] = z
-bench("step_host (env default)", lambda: lib.slb_env_step_host(*args, h_act.data_ptr(), *tail, hr, hd, 100, st))
-bench("env.step_host wrapper", lambda: env.step_host(h_act, h_out[:4 * n].view(torch.int32), h_out[4 * n:]))
-# zero-copy actions only / outputs only
-def zc_in():
-    lib.slb_env_step(*args, h_act.data_ptr(), *tail, env._reward.data_ptr(), env._done.data_ptr(), 100, st)
-    torch.cuda.current_stream().synchronize()
-bench("kernel reads pinned actions, dev outputs", zc_in)
-def zc_out():
-    lib.slb_env_step(*args, acts.data_ptr(), *tail, hr, hd, 100, st)
-    torch.cuda.current_stream().synchronize()
-bench("dev actions, kernel writes pinned outputs", zc_out)
+def pipelined(depth, steps, same_batch=False):
+    streams = ALL_STREAMS[:depth]
+    t_step = t_wait = 0.0
+
+    def loop(count, timed):
+        nonlocal t_step, t_wait
+        for i in range(count):
+            s = i % depth
+            e = envs[0 if same_batch else i % nb]
+            a = pc()
+            if i >= depth:
+                e.wait(streams[s])
+            b = pc()
+            e.step_host(ap, op[s][0], op[s][1], sync=False, stream=streams[s])
+            c = pc()
+            if timed:
+                t_wait += b - a
+                t_step += c - b
+        for s in range(depth):
+            envs[0].wait(streams[s])
+
+    loop(2 * nb + depth, False)
+    t0 = pc()
+    loop(steps, True)
+    dt = pc() - t0
+    print("depth %d%s: %6.2f us/step  (in step call %5.2f, in wait %5.2f)  -> %.0f M env-steps/s" % (
+        depth, " same batch" if same_batch else "", dt / steps * 1e6, t_step / steps * 1e6, t_wait / steps * 1e6,
+        n * steps / dt / 1e6))
+
+
+print("SLB_HOST_GRAPH=%s n=%d batches=%d" % (os.environ.get("SLB_HOST_GRAPH", "1"), n, nb))
+for depth in (1, 2, 3, 4):
+    pipelined(depth, 2000)
+pipelined(2, 2000, same_batch=True)

@@ -479,3 +479,63 @@ def test_benchmark_log_golden(sl, tmp_path):
         assert head(text.split("---\n", 1)[1]) == head(want_txt)
         stats = bm.load_benchmarks(log)
         assert stats["length"].tolist() == [want["length"]] and set(stats["side effects"]) == set(want["side effects"])
+
+
+def test_step_host_paths_agree(sl):
+    """slb_env_step_host(_async) / slb_stepper_*: the plain path (default stream), the cached-graph
+    path (side streams, pageable AND pinned buffers, more env batches than graph-cache entries) and
+    the device-buffer step give identical rewards, dones and states."""
+    lv = gu.levels("prune-spawn")
+    pool = sl.game.LevelPool(lv)
+    n, T, nb = 96, 12, 20  # 20 batches > 16 cached graphs per stream
+    rng = np.random.RandomState(7)
+    acts = rng.randint(9, size=(T, nb, n)).astype(np.uint8)
+
+    def make():
+        out = []
+        for b in range(nb):
+            e = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=b * n, global_counter=None, compute_obs=False,
+                                   auto_reset=True, time_limit=7)
+            e.seed(5); e.reset()
+            out.append(e)
+        return out
+
+    ref, plain, graphed = make(), make(), make()
+    want_r = np.zeros((T, nb, n), np.int32); want_d = np.zeros((T, nb, n), np.uint8)
+    for t in range(T):
+        for b in range(nb):
+            _, r, d, _ = ref[b].step(torch.from_numpy(acts[t, b]).cuda())
+            want_r[t, b] = r.cpu().numpy(); want_d[t, b] = d.cpu().numpy()
+    # plain path: default stream, synchronous
+    r = np.zeros(n, np.int32); d = np.zeros(n, np.uint8)
+    for t in range(T):
+        for b in range(nb):
+            plain[b].step_host(acts[t, b], r, d)
+            assert (r == want_r[t, b]).all() and (d == want_d[t, b]).all()
+    # cached-graph path: two side streams, results waited for one step later
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [(np.zeros(n, np.int32), np.zeros(n, np.uint8)),
+            (torch.zeros(n, dtype=torch.int32).pin_memory(), torch.zeros(n, dtype=torch.uint8).pin_memory())]
+    pending = [None, None]
+    k = 0
+    for t in range(T):
+        for b in range(nb):
+            s = k % 2
+            if pending[s] is not None:
+                graphed[0].wait(streams[s])
+                pt, pb = pending[s]
+                assert (np.asarray(outs[s][0]) == want_r[pt, pb]).all()
+                assert (np.asarray(outs[s][1]) == want_d[pt, pb]).all()
+            graphed[b].step_host(acts[t, b], outs[s][0], outs[s][1], sync=False, stream=streams[s])
+            pending[s] = (t, b)
+            k += 1
+    for s in range(2):
+        graphed[0].wait(streams[s])
+        pt, pb = pending[s]
+        assert (np.asarray(outs[s][0]) == want_r[pt, pb]).all()
+    torch.cuda.synchronize()
+    for b in range(nb):
+        for other in (plain, graphed):
+            assert (other[b].game.state == ref[b].game.state).all()
+            assert (other[b].game.board == ref[b].game.board).all()
+            assert (other[b].game.goals == ref[b].game.goals).all()
