@@ -23,7 +23,10 @@
 
 namespace slb {
 
-constexpr int RES_WARPS = 4;  // warps (= envs) per CTA
+#ifndef SLB_RES_WARPS
+#define SLB_RES_WARPS 4
+#endif
+constexpr int RES_WARPS = SLB_RES_WARPS;  // warps (= envs) per CTA
 
 inline bool fast_shape(int h, int w) { return h >= 4 && w >= 4 && h <= 32 && w <= 32; }
 
@@ -149,8 +152,9 @@ __device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, c
 // GB / GG: compile-time plane-group masks of boards / goals (supersets of pool.plane_groups):
 // planes of absent groups are constant zero, so their registers and all work on them fold away.
 // HW: board height = width when known at compile time (26: the benchmark levels), 0 = run time.
-template <unsigned GB, unsigned GG, int HW>
-__global__ void __launch_bounds__(RES_WARPS * 32, 7)
+// ONE: exactly one step per launch (the policy-in-the-loop case): no step loop, no action look-ahead.
+template <unsigned GB, unsigned GG, int HW, bool ONE>
+__global__ void __launch_bounds__(RES_WARPS * 32, 28 / RES_WARPS)
 res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                        const uint8_t *__restrict__ actions, int t_steps, int time_limit,
                        uint64_t seed, uint64_t env_id0, int32_t *reward_out, uint8_t *done_out,
@@ -170,23 +174,30 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
         // (one 128-byte line per lane).  L2 is the point of coherence, so a line prefetched before
         // the previous kernel's last writes land still reads back current after the wait below.
         const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
-        const char *pf = nullptr;
-        if (lane < nb) pf = (const char *)bp + lane * 128;
-        else if (lane < nb + ng) pf = (const char *)gp + (lane - nb) * 128;
-        else if (lane == nb + ng) pf = (const char *)(state + i);
-        if (pf) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+        const bool in_b = lane < nb;
+        const char *pf = (const char *)(in_b ? bp : gp) + (in_b ? lane : lane - nb) * 128;
+        if (lane == nb + ng) pf = (const char *)(state + i);
+        if (lane <= nb + ng) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
-    int action = actions[i];
+    actions += i;
+    if (reward_out) reward_out += i;
+    if (done_out) done_out += i;
+    int action = *actions;
     load_res(bp, g, GB, B);
     load_res(gp, g, GG, G);
     LevelConsts lc = load_level(pool, e.level, g);
     const uint64_t env = env_id0 + (uint64_t)i;
     bool g_dirty = false;
+    const int steps = ONE ? 1 : t_steps;
 
-    for (int t = 0; t < t_steps; t++) {
-        const int next_action = (t + 1 < t_steps) ? actions[(size_t)(t + 1) * n + i] : 0;
+    for (int t = 0; t < steps; t++) {
+        int next_action = 0;
+        if (!ONE) {
+            actions += n;
+            if (t + 1 < steps) next_action = *actions;
+        }
         bool touched, ch;
         int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched);
         // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
@@ -202,8 +213,12 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
         const int done = (e.ep_len > time_limit) || e.game_over;
         e.ep_done = done;
         if (lane == 0) {
-            if (reward_out) reward_out[(size_t)t * n + i] = reward;
-            if (done_out) done_out[(size_t)t * n + i] = (uint8_t)done;
+            if (reward_out) *reward_out = reward;
+            if (done_out) *done_out = (uint8_t)done;
+        }
+        if (!ONE) {
+            if (reward_out) reward_out += n;
+            if (done_out) done_out += n;
         }
         if (done && auto_reset_stride > 0) {
             reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
@@ -237,9 +252,15 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
     cfg.stream = st;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
+#define SLB_ROLL3(GBV, GGV, HWV, ONEV)                                                               \
+    cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV, HWV, ONEV>, pool, n, board, goals,      \
+                       state, actions, t_steps, time_limit, seed, env0, reward, done, stride,         \
+                       l2_prefetch)
 #define SLB_ROLL2(GBV, GGV, HWV)                                                                     \
-    cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV, HWV>, pool, n, board, goals, state,     \
-                       actions, t_steps, time_limit, seed, env0, reward, done, stride, l2_prefetch)
+    do {                                                                                             \
+        if (t_steps == 1) SLB_ROLL3(GBV, GGV, HWV, true);                                            \
+        else SLB_ROLL3(GBV, GGV, HWV, false);                                                        \
+    } while (0)
 #define SLB_ROLL(GBV, GGV)                                                                           \
     do {                                                                                             \
         if (pool.h == 26 && pool.w == 26) SLB_ROLL2(GBV, GGV, 26);                                   \
@@ -248,6 +269,7 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
     if (!(gg & ~3u) && !(gb & ~7u)) SLB_ROLL(7u, 3u);        // no spawners anywhere, plain goals
     else if (!(gg & ~3u)) SLB_ROLL(15u, 3u);                 // spawners on the boards, plain goals
     else SLB_ROLL(15u, 15u);
+#undef SLB_ROLL3
 #undef SLB_ROLL2
 #undef SLB_ROLL
 }
