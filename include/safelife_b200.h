@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SLB_ABI_VERSION 2
+#define SLB_ABI_VERSION 3
 
 typedef enum {
     SLB_OK = 0,
@@ -83,7 +83,29 @@ typedef struct {
                                        zeroed by the caller, maintained by slb_pool_prepare / _import */
     uint32_t plane_groups[2];       /* host copy as plane-group masks (bit g = group g in use) for boards /
                                        goals; written by slb_pool_prepare and slb_resident_import */
+    void *level_consts;             /* [P] 32-byte slb_level_consts records, written by slb_pool_prepare */
+    uint32_t external_writes;       /* host flag, set by slb_resident_import into an env buffer and by the
+                                       single-stage calls (slb_execute_action, slb_game_advance,
+                                       slb_update_exit_colors): some env's board / goals were written
+                                       outside the fused step and reset, so the fused step may no longer
+                                       assume that an env's goals equal its level's or that the score kept
+                                       in slb_env_state matches the board; it then recomputes both every
+                                       step (always exact either way) */
+    uint32_t reserved;
 } slb_pool;
+
+/* What the step kernels read per level, packed so that it arrives with two 16-byte loads. */
+typedef struct {
+    float spawn_prob;
+    int32_t baseline;
+    uint32_t flags;                 /* SLB_LEVEL_GOALS_STATIC */
+    uint32_t pad0;
+    double min_performance;
+    uint64_t pad1;
+} slb_level_consts;
+/* the level's goals board is a fixed point of advance_board and holds no spawner: it never changes
+ * (no action touches goals), so an env that plays the level need not advance it */
+#define SLB_LEVEL_GOALS_STATIC 1u
 
 /* ---- RESIDENT env state ------------------------------------------------------------------------
  * Between steps an env's board and goals live on the device in the layout the kernels compute in,
@@ -137,12 +159,12 @@ int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const
  * d_actions: [N] uint8, 0 NULL, 1-4 MOVE U/R/D/L, 5-8 TOGGLE U/R/D/L (safelife_env.py:61-71).
  * Uses and updates d_state (agent_x/y, orientation, game_over); can_exit is read from
  * d_state[i].can_exit.  d_reward: [N] int32 action reward (0 / +1). */
-int slb_execute_action(const slb_pool *pool, int n, void *d_board, slb_env_state *d_state,
+int slb_execute_action(slb_pool *pool, int n, void *d_board, slb_env_state *d_state,
                        const uint8_t *d_actions, int32_t *d_reward, void *stream);
 
 /* ---- A4: SafeLifeGame.advance_board (safelife_game.py:657-660) on resident state: num_steps += 1,
  * board then goals (the order the env's stream is consumed in), spawn_prob of each env's level. */
-int slb_game_advance(const slb_pool *pool, int n, void *d_board, void *d_goals,
+int slb_game_advance(slb_pool *pool, int n, void *d_board, void *d_goals,
                      slb_env_state *d_state, uint64_t seed, uint64_t env_id0, void *stream);
 
 /* ---- A9-A11: current_points, performance_ratio, can_exit (safelife_game.py:590-631, 522-526) ----
@@ -155,7 +177,7 @@ int slb_points_and_performance(const slb_pool *pool, int n, const void *d_board,
 /* update_exit_colors (safelife_game.py:531-537): evaluates can_exit() on the current board/goals,
  * repaints the level's initial exit cells (272 / 784) and refreshes d_state[i].can_exit,
  * .completed, .possible. */
-int slb_update_exit_colors(const slb_pool *pool, int n, void *d_board, const void *d_goals,
+int slb_update_exit_colors(slb_pool *pool, int n, void *d_board, const void *d_goals,
                            slb_env_state *d_state, void *stream);
 
 /* ---- A12: one SafeLifeEnv.step for N envs, fused (safelife_env.py:157-186) ----------------------

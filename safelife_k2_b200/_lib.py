@@ -33,6 +33,7 @@ class Pool(C.Structure):
         ("baseline", C.c_void_p), ("exit_mask", C.c_void_p),
         ("board_res", C.c_void_p), ("goals_res", C.c_void_p), ("plane_bits", C.c_void_p),
         ("plane_groups", C.c_uint32 * 2),
+        ("level_consts", C.c_void_p), ("external_writes", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
@@ -88,7 +89,7 @@ def load():
             fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
             fn.restype = res
             fn.argtypes = args
-        if lib.slb_abi_version() != 2:
+        if lib.slb_abi_version() != 3:
             raise ImportError("libsafelife_b200.so ABI version mismatch")
         _lib = lib
     return _lib

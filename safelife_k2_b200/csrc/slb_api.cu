@@ -54,7 +54,8 @@ int check_pool(const slb_pool *p) {
     if (p->n_levels <= 0) return fail(SLB_ERR_INVALID, "pool has no levels");
     if (p->words_per_row != (p->w + 31) / 32) return fail(SLB_ERR_INVALID, "pool.words_per_row");
     if (!p->board || !p->goals || !p->agent_x || !p->agent_y || !p->orientation ||
-        !p->spawn_prob || !p->min_performance || !p->baseline || !p->exit_mask || !p->plane_bits)
+        !p->spawn_prob || !p->min_performance || !p->baseline || !p->exit_mask || !p->plane_bits ||
+        !p->level_consts)
         return fail(SLB_ERR_INVALID, "pool has NULL arrays");
     if ((fast_shape(p->h, p->w) || big_shape(p->h, p->w)) && (!p->board_res || !p->goals_res))
         return fail(SLB_ERR_INVALID, "pool.board_res / goals_res are required for %dx%d boards", p->h, p->w);
@@ -131,6 +132,8 @@ int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int 
         return fail(SLB_ERR_INVALID, "slb_resident_import: pool / which do not match the boards");
     uint32_t *pool_plane_bits = pool ? pool->plane_bits + which : nullptr;
     if (n == 0) return SLB_OK;
+    // an env buffer written from outside: the fused step stops trusting its cached score / static goals
+    if (pool && d_res != pool->board_res && d_res != pool->goals_res) pool->external_writes = 1;
     cudaStream_t st = (cudaStream_t)stream;
     if (big_shape(h, w)) {
         if ((uintptr_t)d_res % 16 || (uintptr_t)d_cells % 16)
@@ -185,6 +188,12 @@ int slb_pool_prepare(slb_pool *pool, void *stream) {
         if (int rc = slb_resident_import(pool->goals, pool->goals_res, pool->n_levels, pool->h, pool->w,
                                          pool, 1, stream)) return rc;
     }
+    if (fast_shape(pool->h, pool->w)) {
+        res_level_flags_kernel<<<(pool->n_levels + RES_WARPS - 1) / RES_WARPS, RES_WARPS * 32, 0,
+                                 (cudaStream_t)stream>>>(*pool);
+        SLB_LAUNCHED();
+    }
+    pool->external_writes = 0;
     return SLB_OK;
 }
 
@@ -291,12 +300,13 @@ int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const
     return SLB_OK;
 }
 
-int slb_execute_action(const slb_pool *pool, int n, void *d_board, slb_env_state *d_state,
+int slb_execute_action(slb_pool *pool, int n, void *d_board, slb_env_state *d_state,
                        const uint8_t *d_actions, int32_t *d_reward, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_board || !d_state || !d_actions)
         return fail(SLB_ERR_INVALID, "slb_execute_action: bad arguments");
     if (n == 0) return SLB_OK;
+    pool->external_writes = 1;  // a board written outside the fused step (see slb_pool)
     if (fast_shape(pool->h, pool->w)) {
         res_action_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(*pool, n, (uint32_t *)d_board, d_state,
                                                                d_actions, d_reward);
@@ -312,12 +322,13 @@ int slb_execute_action(const slb_pool *pool, int n, void *d_board, slb_env_state
     return SLB_OK;
 }
 
-int slb_game_advance(const slb_pool *pool, int n, void *d_board, void *d_goals,
+int slb_game_advance(slb_pool *pool, int n, void *d_board, void *d_goals,
                      slb_env_state *d_state, uint64_t seed, uint64_t env_id0, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_board || !d_goals || !d_state)
         return fail(SLB_ERR_INVALID, "slb_game_advance: bad arguments");
     if (n == 0) return SLB_OK;
+    pool->external_writes = 1;  // a board written outside the fused step (see slb_pool)
     cudaStream_t st = (cudaStream_t)stream;
     if (fast_shape(pool->h, pool->w)) {
         res_advance_kernel<<<RES_GRID(n), st>>>(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals,
@@ -363,12 +374,13 @@ int slb_points_and_performance(const slb_pool *pool, int n, const void *d_board,
     return SLB_OK;
 }
 
-int slb_update_exit_colors(const slb_pool *pool, int n, void *d_board, const void *d_goals,
+int slb_update_exit_colors(slb_pool *pool, int n, void *d_board, const void *d_goals,
                            slb_env_state *d_state, void *stream) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_board || !d_goals || !d_state)
         return fail(SLB_ERR_INVALID, "slb_update_exit_colors: bad arguments");
     if (n == 0) return SLB_OK;
+    pool->external_writes = 1;  // a board written outside the fused step (see slb_pool)
     if (fast_shape(pool->h, pool->w))
         res_score_kernel<true><<<RES_GRID(n), (cudaStream_t)stream>>>(
             *pool, n, (uint32_t *)d_board, (const uint32_t *)d_goals, d_state, nullptr, nullptr, nullptr, nullptr);

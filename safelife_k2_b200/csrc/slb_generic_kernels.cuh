@@ -50,7 +50,15 @@ __global__ void __launch_bounds__(GEN_THREADS) pool_prepare_kernel(slb_pool pool
         cur += s.current;
     }
     block_sum3(pts, cur, pos, scratch);
-    if (threadIdx.x == 0) pool.baseline[l] = cur;
+    if (threadIdx.x == 0) {
+        pool.baseline[l] = cur;
+        slb_level_consts rec = {};
+        rec.spawn_prob = pool.spawn_prob[l];
+        rec.baseline = cur;
+        rec.flags = 0u;  // res_level_flags_kernel adds SLB_LEVEL_GOALS_STATIC on fast-path shapes
+        rec.min_performance = pool.min_performance[l];
+        reinterpret_cast<slb_level_consts *>(pool.level_consts)[l] = rec;
+    }
 }
 
 // CTA-wide reset of one env from the pool (safelife_env.py:188-198).  Every thread must call.

@@ -131,6 +131,20 @@ __device__ __forceinline__ int action_planes(uint32_t P[16], const Geo &g, int &
     return reward;
 }
 
+// The same, also reporting whether the action changed what the score reads.  The score only looks
+// at alive cells; an action creates, destroys or moves whole cells, and every such change of an
+// alive cell flips the alive plane somewhere (the agent is not alive, and a moving cell only ever
+// lands on an empty cell, on the agent's old place or on a cell that is overwritten), so comparing
+// the alive plane before and after is exact.
+__device__ __forceinline__ int action_planes(uint32_t P[16], const Geo &g, int &ax, int &ay,
+                                             int &orientation, int &game_over, int action,
+                                             int can_exit, bool &touched, bool &life_touched) {
+    const uint32_t a0 = P[0];
+    const int reward = action_planes(P, g, ax, ay, orientation, game_over, action, can_exit, touched);
+    life_touched = touched && __any_sync(FULL, a0 != P[0]);
+    return reward;
+}
+
 // ---------------------------------------------------------------------------------------------
 // current_points / performance_ratio on planes (safelife_game.py:554-565, 590-631).
 // Returns this lane's row sums; the caller warp-reduces.

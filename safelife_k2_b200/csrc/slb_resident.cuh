@@ -100,17 +100,23 @@ __device__ __forceinline__ void store_env(slb_env_state *s, const EnvRegs &e) {
 struct LevelConsts {
     float spawn_prob;
     int baseline;
+    uint32_t flags;
     double min_perf;
     uint32_t e0;  // this lane's row of the level's initial exit cells
 };
 
+// pool.level_consts: one 32-byte slb_level_consts record per level, two 16-byte loads
 __device__ __forceinline__ LevelConsts load_level(const slb_pool &pool, int level, const Geo &g) {
     LevelConsts c;
     const int lane = threadIdx.x & 31;
-    c.spawn_prob = pool.spawn_prob[level];
-    c.baseline = pool.baseline[level];
-    c.min_perf = pool.min_performance[level];
-    c.e0 = g.row ? pool.exit_mask[(size_t)level * g.h + lane] : 0u;
+    const uint4 *rec = reinterpret_cast<const uint4 *>(pool.level_consts) + 2 * level;
+    const uint4 a = rec[0];
+    const uint2 b = *reinterpret_cast<const uint2 *>(rec + 1);
+    c.spawn_prob = __uint_as_float(a.x);
+    c.baseline = (int)a.y;
+    c.flags = pool.external_writes ? 0u : a.z;
+    c.min_perf = __hiloint2double((int)b.y, (int)b.x);
+    c.e0 = g.row ? pool.exit_mask[level * g.h + lane] : 0u;
     return c;
 }
 
@@ -198,16 +204,24 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
             actions += n;
             if (t + 1 < steps) next_action = *actions;
         }
-        bool touched, ch;
-        int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched);
+        bool touched, life_touched, ch_b, ch_g = false;
+        int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
+                                   life_touched);
         // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
         e.num_steps += 1;
-        e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch);
-        e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch);
-        g_dirty |= ch;
-        const int pts = score_and_paint(B, G, g, lc, e, true);
-        reward += pts - e.old_points;
-        e.old_points = pts;
+        e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch_b);
+        if (!(lc.flags & SLB_LEVEL_GOALS_STATIC))  // a static goals board is its own successor
+            e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch_g);
+        g_dirty |= ch_g;
+        // The score reads alive cells (their colour, frozen / movable bits) and goal colours.  When
+        // the action moved no living cell and neither board changed, points, completed, possible
+        // and can_exit are what they were, and the exit cells (frozen, never overwritten by an
+        // action) still carry the colour painted for that can_exit.
+        if (life_touched || ch_b || ch_g || pool.external_writes) {
+            const int pts = score_and_paint(B, G, g, lc, e, true);
+            reward += pts - e.old_points;
+            e.old_points = pts;
+        }
         e.ep_len += 1;
         e.ep_reward += reward;
         const int done = (e.ep_len > time_limit) || e.game_over;
@@ -272,6 +286,23 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
 #undef SLB_ROLL3
 #undef SLB_ROLL2
 #undef SLB_ROLL
+}
+
+// pool prepare, after the resident copies exist: which levels have goals that never change
+// (a fixed point of advance_board without spawners; safelife_game.py:657-660 advances goals too)
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_level_flags_kernel(slb_pool pool) {
+    const int lane = threadIdx.x & 31;
+    const int l = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (l >= pool.n_levels) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    uint32_t G[16];
+    load_res((const uint32_t *)pool.goals_res + l * resident_words(g.h), g, 15u, G);
+    const bool spawners = __any_sync(FULL, G[7] != 0);
+    bool changed;
+    physics_planes(G, g, 0.0f, 0, 0, 0, changed);
+    if (lane == 0 && !spawners && !changed)
+        reinterpret_cast<slb_level_consts *>(pool.level_consts)[l].flags |= SLB_LEVEL_GOALS_STATIC;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -118,13 +118,14 @@ class LevelPool(object):
         self.board_res = torch.zeros(P * self.resident_bytes, dtype=torch.uint8, device=self.device)
         self.goals_res = torch.zeros_like(self.board_res)
         self.plane_bits = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.level_consts = torch.zeros((P, 32), dtype=torch.uint8, device=self.device)  # slb_level_consts
         self.c = _lib.Pool(P, H, W, self.words_per_row, self.board.data_ptr(), self.goals.data_ptr(),
                            self.agent_x.data_ptr(), self.agent_y.data_ptr(),
                            self.orientation.data_ptr(), self.spawn_prob.data_ptr(),
                            self.min_performance.data_ptr(), self.baseline.data_ptr(),
                            self.exit_mask.data_ptr(), self.board_res.data_ptr(),
                            self.goals_res.data_ptr(), self.plane_bits.data_ptr(),
-                           (C.c_uint32 * 2)(0, 0))
+                           (C.c_uint32 * 2)(0, 0), self.level_consts.data_ptr(), 0, 0)
         with torch.cuda.device(self.device):
             _lib.check(_lib.load().slb_pool_prepare(self.c, _lib.current_stream()))
 

@@ -539,3 +539,73 @@ def test_step_host_paths_agree(sl):
             assert (other[b].game.state == ref[b].game.state).all()
             assert (other[b].game.board == ref[b].game.board).all()
             assert (other[b].game.goals == ref[b].game.goals).all()
+
+
+def test_out_of_band_writes_keep_the_step_exact(sl):
+    """The fused step keeps each env's score (and, for levels whose goals never change, skips the goals
+    physics) as long as boards are only written by the step and reset.  Writing a board or goals from
+    outside (board/goals setters, single-stage calls) must switch that off: every later step still
+    equals the oracle, which rescans every step like the reference."""
+    lv = gu.levels("append-still")
+    pool = sl.game.LevelPool(lv)
+    n = 128
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False)
+    env.seed(2); env.reset()
+    lvl = np.arange(n) % pool.n_levels
+    oenv = slo.OracleBatchEnv(slo.OraclePool(**lv), lvl, seed=2, threads=4)
+    rng = np.random.RandomState(11)
+
+    def step(acts):
+        _, r, d, _ = env.step(acts)
+        orr, od = oenv.step(acts)
+        assert (r.cpu().numpy() == orr).all() and (d.cpu().numpy() == (od != 0)).all()
+
+    def same():
+        assert (env.game.board.cpu().numpy() == oenv.boards).all()
+        assert (env.game.goals.cpu().numpy() == oenv.goals).all()
+        st, ost = env.game.state_numpy(), oenv.states
+        for f in st.dtype.names:
+            assert (st[f] == ost[f]).all(), f
+
+    for _ in range(12):
+        step(rng.randint(9, size=n))
+    same()
+    assert pool.c.external_writes == 0
+    # 1. boards replaced from outside: a green still life block dropped into every even env, then idle steps
+    b = oenv.boards.copy()
+    b[::2, 1:3, 1:3] = 1033
+    oenv.boards[:] = b
+    env.game.board = torch.from_numpy(b).cuda()
+    assert pool.c.external_writes == 1
+    for _ in range(3):
+        step(np.zeros(n, int))
+    same()
+    # 2. goals replaced from outside (an oscillator: the goals of these levels stop being static)
+    g = oenv.goals.copy()
+    g[1::2, 5, 4:7] = 1 | (2 << 9)
+    oenv.goals[:] = g
+    env.game.goals = torch.from_numpy(g).cuda()
+    for _ in range(4):
+        step(np.zeros(n, int))
+    for _ in range(10):
+        step(rng.randint(9, size=n))
+    same()
+    # 3. a fresh pool, single-stage calls between fused steps
+    pool2 = sl.game.LevelPool(lv)
+    env2 = sl.env.SafeLifeEnv(pool2, num_envs=n, global_counter=None, compute_obs=False)
+    env2.seed(2); env2.reset()
+    o2 = slo.OracleBatchEnv(slo.OraclePool(**lv), lvl, seed=2, threads=4)
+    acts = rng.randint(5, 9, size=n)  # toggles: create / destroy life in front of the agent
+    env2.game.execute_action(acts)
+    for i in range(n):
+        slo.execute_action(o2.boards[i], o2.states[i:i + 1], acts[i], o2.states["can_exit"][i])
+    assert pool2.c.external_writes == 1
+    for _ in range(3):
+        a = np.zeros(n, int)
+        _, r, d, _ = env2.step(a)
+        orr, od = o2.step(a)
+        assert (r.cpu().numpy() == orr).all()
+    assert (env2.game.board.cpu().numpy() == o2.boards).all()
+    st, ost = env2.game.state_numpy(), o2.states
+    for f in st.dtype.names:
+        assert (st[f] == ost[f]).all(), f
