@@ -261,9 +261,19 @@ int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_
 int slb_side_effect_penalty(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
                             const slb_env_state *d_state, int32_t *d_count, void *stream);
 
+/* get_obs with the channel split fused in (safelife_env.py:125-155 in one call): d_out uint16
+ * [N, vh, vw, n_channels], 16-byte aligned; h_channels as for slb_obs_channels.  Boards of 4..32 rows /
+ * columns with vh * vw <= 1104 run as ONE kernel; any other shape goes through slb_get_obs +
+ * slb_obs_channels and needs d_words_scratch (uint16 [N, vh, vw]; SLB_ERR_UNSUPPORTED if it is NULL). */
+int slb_get_obs_channels(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
+                         const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
+                         const uint8_t *h_channels, int n_channels, uint16_t *d_words_scratch,
+                         uint16_t *d_out, void *stream);
+
 /* The channel split of safelife_env.py:152-154 for M packed words: d_out [M, n_channels] uint16,
- * d_out[m, c] = (d_words[m] >> d_channels[c]) & 1.  n_channels <= 16; d_out 4-byte aligned. */
-int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *d_channels, int n_channels,
+ * d_out[m, c] = (d_words[m] >> h_channels[c]) & 1.  h_channels: n_channels <= 16 bit indices in HOST
+ * memory (read before the call returns); d_out 16-byte aligned. */
+int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *h_channels, int n_channels,
                      uint16_t *d_out, void *stream);
 
 #ifdef __cplusplus

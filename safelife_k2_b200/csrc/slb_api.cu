@@ -767,9 +767,9 @@ int slb_get_obs(const slb_pool *pool, int n, const void *d_board, const void *d_
         return fail(SLB_ERR_INVALID, "slb_get_obs: bad arguments");
     if (n == 0) return SLB_OK;
     if (fast_shape(pool->h, pool->w))
-        res_obs_kernel<<<RES_GRID(n), (cudaStream_t)stream>>>(
+        res_obs_kernel<false, true><<<RES_GRID(n), (cudaStream_t)stream>>>(
             *pool, n, (const uint32_t *)d_board, (const uint32_t *)d_goals, d_state, vh, vw,
-            remove_white_goals, d_obs);
+            remove_white_goals, ObsChannels{}, 0, d_obs);
     else if (big_shape(pool->h, pool->w))
         big_obs_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(*pool, (const uint32_t *)d_board,
                                                           (const uint32_t *)d_goals, d_state, vh, vw,
@@ -802,17 +802,66 @@ int slb_side_effect_penalty(const slb_pool *pool, int n, const void *d_board, co
     return SLB_OK;
 }
 
-int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *d_channels, int n_channels,
+static int obs_table(const uint8_t *h_channels, int n_channels, ObsChannels *t, bool *ident) {
+    if (!h_channels || n_channels < 1 || n_channels > 16)
+        return fail(SLB_ERR_INVALID, "observation channels: 1..16 bit indices expected");
+    *t = ObsChannels{};
+    *ident = true;
+    for (int c = 0; c < n_channels; c++) {
+        if (h_channels[c] > 15) return fail(SLB_ERR_INVALID, "observation channel %d is not a bit index", c);
+        t->ch[c] = h_channels[c];
+        *ident = *ident && h_channels[c] == c;
+    }
+    return SLB_OK;
+}
+
+int slb_get_obs_channels(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
+                         const slb_env_state *d_state, int vh, int vw, int remove_white_goals,
+                         const uint8_t *h_channels, int n_channels, uint16_t *d_words_scratch,
+                         uint16_t *d_out, void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || vh < 1 || vw < 1 || !d_board || !d_goals || !d_state || !d_out)
+        return fail(SLB_ERR_INVALID, "slb_get_obs_channels: bad arguments");
+    ObsChannels t;
+    bool ident;
+    if (int rc = obs_table(h_channels, n_channels, &t, &ident)) return rc;
+    if ((uintptr_t)d_out % 16) return fail(SLB_ERR_INVALID, "slb_get_obs_channels: d_out must be 16-byte aligned");
+    if (n == 0) return SLB_OK;
+    if (fast_shape(pool->h, pool->w) && (long long)vh * vw <= RES_VIEW_U16) {
+        if (ident)
+            res_obs_kernel<true, true><<<RES_GRID(n), (cudaStream_t)stream>>>(
+                *pool, n, (const uint32_t *)d_board, (const uint32_t *)d_goals, d_state, vh, vw,
+                remove_white_goals, t, n_channels, d_out);
+        else
+            res_obs_kernel<true, false><<<RES_GRID(n), (cudaStream_t)stream>>>(
+                *pool, n, (const uint32_t *)d_board, (const uint32_t *)d_goals, d_state, vh, vw,
+                remove_white_goals, t, n_channels, d_out);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    if (!d_words_scratch)
+        return fail(SLB_ERR_UNSUPPORTED, "slb_get_obs_channels: this board / view shape needs d_words_scratch");
+    if (int rc = slb_get_obs(pool, n, d_board, d_goals, d_state, vh, vw, remove_white_goals, d_words_scratch, stream))
+        return rc;
+    return slb_obs_channels(d_words_scratch, (size_t)n * vh * vw, h_channels, n_channels, d_out, stream);
+}
+
+int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *h_channels, int n_channels,
                      uint16_t *d_out, void *stream) {
-    if (!d_words || !d_channels || !d_out || n_channels < 1 || n_channels > 16)
-        return fail(SLB_ERR_INVALID, "slb_obs_channels: bad arguments");
-    if ((uintptr_t)d_out % 4) return fail(SLB_ERR_INVALID, "slb_obs_channels: d_out must be 4-byte aligned");
+    if (!d_words || !d_out) return fail(SLB_ERR_INVALID, "slb_obs_channels: bad arguments");
+    if ((uintptr_t)d_out % 16) return fail(SLB_ERR_INVALID, "slb_obs_channels: d_out must be 16-byte aligned");
+    ObsChannels t;
+    bool ident;
+    if (int rc = obs_table(h_channels, n_channels, &t, &ident)) return rc;
     if (m == 0) return SLB_OK;
-    size_t pairs = (m * (size_t)n_channels + 1) / 2;
-    size_t blocks = (pairs + 255) / 256;
-    if (blocks > 148 * 16) blocks = 148 * 16;
-    obs_channels_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_words, m, d_channels,
-                                                                         n_channels, d_out);
+    size_t chunks = (m * (size_t)n_channels) >> 3;
+    size_t blocks = (chunks + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    if (ident)
+        obs_channels_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_words, m, t, n_channels, d_out);
+    else
+        obs_channels_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_words, m, t, n_channels, d_out);
     SLB_LAUNCHED();
     return SLB_OK;
 }

@@ -180,10 +180,9 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
         // (one 128-byte line per lane).  L2 is the point of coherence, so a line prefetched before
         // the previous kernel's last writes land still reads back current after the wait below.
         const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
-        const bool in_b = lane < nb;
-        const char *pf = (const char *)(in_b ? bp : gp) + (in_b ? lane : lane - nb) * 128;
-        if (lane == nb + ng) pf = (const char *)(state + i);
-        if (lane <= nb + ng) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+        if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)bp + lane * 128));
+        if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)gp + lane * 128));
+        if (lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(state + i));
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
@@ -472,11 +471,30 @@ __device__ __forceinline__ int pymod_w(int a, int m) {
     return r < 0 ? r + m : r;
 }
 
+struct ObsChannels { uint8_t ch[16]; };
+
+template <bool IDENT>
+__device__ __forceinline__ uint32_t obs_remap(uint32_t w, const ObsChannels &t, int c_n) {
+    if (IDENT) return w & ((1u << c_n) - 1u);
+    uint32_t r = 0;
+#pragma unroll
+    for (int c = 0; c < 16; c++)
+        if (c < c_n) r |= ((w >> t.ch[c]) & 1u) << c;
+    return r;
+}
+
+constexpr int RES_VIEW_U16 = 1104;  // largest view the fused channel output stages (33 x 33 = 1089)
+
+// Observation of safelife_env.py:125-155 for one env per warp.  c_n == 0: packed words, obs is
+// uint16 [N, vh, vw].  c_n > 0 (vh * vw <= RES_VIEW_U16): the channel split is fused in, obs is
+// uint16 [N, vh, vw, c_n] and is written with 16-byte stores (obs must be 16-byte aligned).
+template <bool CHANNELS, bool IDENT>
 __global__ void __launch_bounds__(RES_WARPS * 32)
 res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
                const uint32_t *__restrict__ goals, const slb_env_state *__restrict__ state, int vh,
-               int vw, int remove_white, uint16_t *obs) {
+               int vw, int remove_white, ObsChannels tab, int c_n, uint16_t *obs) {
     __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
+    __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? RES_VIEW_U16 : 8];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i = blockIdx.x * RES_WARPS + warp;
     if (i >= n) return;
@@ -517,12 +535,15 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
     const slb_env_state *st = state + i;
     const int x0 = st->agent_x, y0 = st->agent_y, level = st->level_id;
     const int x1 = x0 - vw / 2, y1 = y0 - vh / 2;
-    uint16_t *o = obs + (size_t)i * vh * vw;
+    const int V = vh * vw;
+    // the view goes to global memory (packed words) or to shared memory in channel order
+    uint16_t *o = CHANNELS ? view_sm[warp] : obs + (size_t)i * V;
     int vy = 0, vx = lane;  // (vy, vx) of flat index k = lane, advanced by 32 per iteration
     while (vx >= vw) { vx -= vw; vy++; }
     int sy = pymod_w(y1 + vy, h), sx = pymod_w(x1 + vx, w);
-    for (int k = lane; k < vh * vw; k += 32) {
-        o[k] = sm[sy * S + sx];
+    for (int k = lane; k < V; k += 32) {
+        const uint32_t v = sm[sy * S + sx];
+        o[k] = CHANNELS ? (uint16_t)obs_remap<IDENT>(v, tab, c_n) : (uint16_t)v;
         vx += 32;
         while (vx >= vw) { vx -= vw; vy++; }
         sy = pymod_w(y1 + vy, h);
@@ -543,34 +564,83 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
             int jx = pymod_w(x - x0 + w / 2, w) - w / 2;
             jy = min(max(jy + vh / 2, 0), vh - 1);
             jx = min(max(jx + vw / 2, 0), vw - 1);
-            if (lane == 0) o[jy * vw + jx] = sm[y * S + x];
+            if (lane == 0) {
+                const uint32_t v = sm[y * S + x];
+                o[jy * vw + jx] = CHANNELS ? (uint16_t)obs_remap<IDENT>(v, tab, c_n) : (uint16_t)v;
+            }
         }
+    }
+    if (!CHANNELS) return;
+    __syncwarp();
+    // channel split: element e of this env (e = m * c_n + c) is bit c of o[m].  The env's T = V * c_n
+    // output elements start at global element E0 = i * T, which is only 2-byte aligned in general:
+    // single stores up to the first 16-byte boundary, 16-byte stores, single stores for the rest.
+    const uint32_t T = (uint32_t)V * (uint32_t)c_n;
+    const size_t E0 = (size_t)i * T;
+    const uint32_t head = min((uint32_t)((8 - (E0 & 7)) & 7), T);  // elements before the boundary
+    const uint32_t chunks = (T - head) >> 3;
+    const uint32_t tail0 = head + (chunks << 3);
+    uint16_t *out = obs + E0;
+    for (uint32_t e = lane; e < head + (T - tail0); e += 32) {
+        const uint32_t l = e < head ? e : tail0 + (e - head);
+        const uint32_t m = l / (uint32_t)c_n;
+        out[l] = (uint16_t)((o[m] >> (l - m * c_n)) & 1u);
+    }
+    uint4 *out4 = reinterpret_cast<uint4 *>(out + head);
+    for (uint32_t q = lane; q < chunks; q += 32) {
+        const uint32_t l = head + (q << 3);
+        uint32_t m = l / (uint32_t)c_n;
+        const int c0 = (int)(l - m * c_n);
+        uint32_t bits = (uint32_t)o[m] >> c0;
+        for (int have = c_n - c0; have < 8; have += c_n) bits |= (uint32_t)o[++m] << have;
+        uint4 v;
+        v.x = (bits & 1u) | ((bits << 15) & 0x10000u);
+        v.y = ((bits >> 2) & 1u) | ((bits << 13) & 0x10000u);
+        v.z = ((bits >> 4) & 1u) | ((bits << 11) & 0x10000u);
+        v.w = ((bits >> 6) & 1u) | ((bits << 9) & 0x10000u);
+        out4[q] = v;
     }
 }
 
 // packed observation words [M] -> boolean channels [M, C] uint16 (safelife_env.py:152-154):
-// out[m*C + c] = (words[m] >> channels[c]) & 1.  Flat over 32-bit output words, any alignment of M*C.
+// out[m*C + c] = (words[m] >> channels[c]) & 1.  HBM-write bound (2*C bytes out per 2 bytes in): every
+// thread produces 8 consecutive outputs as one 16-byte store.  A cell's C output bits are first
+// gathered into the low bits of one word ("channel order"; the identity when channels = 0..C-1), so
+// the 8 outputs are 8 consecutive bits of the concatenation of successive cells.
+template <bool IDENT>
 __global__ void __launch_bounds__(256)
-obs_channels_kernel(const uint16_t *__restrict__ words, size_t m_words, const uint8_t *__restrict__ channels,
-                    int n_channels, uint16_t *out) {
-    __shared__ uint8_t ch[16];
-    if (threadIdx.x < 16) ch[threadIdx.x] = threadIdx.x < n_channels ? channels[threadIdx.x] : 0;
-    __syncthreads();
-    const size_t total = m_words * (size_t)n_channels;  // uint16 elements
-    const size_t pairs = (total + 1) >> 1;
-    uint32_t *out32 = reinterpret_cast<uint32_t *>(out);
-    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < pairs; q += (size_t)gridDim.x * blockDim.x) {
-        const size_t e0 = 2 * q;
-        const size_t m0 = e0 / n_channels;
-        const int c0 = (int)(e0 - m0 * n_channels);
-        uint32_t v = (words[m0] >> ch[c0]) & 1u;
-        if (e0 + 1 < total) {
-            const int c1 = (c0 + 1 == n_channels) ? 0 : c0 + 1;
-            const size_t m1 = (c0 + 1 == n_channels) ? m0 + 1 : m0;
-            v |= ((words[m1] >> ch[c1]) & 1u) << 16;
-            out32[q] = v;
+obs_channels_kernel(const uint16_t *__restrict__ words, size_t m_words, ObsChannels t, int c_n, uint16_t *out) {
+    const size_t total = m_words * (size_t)c_n;  // uint16 elements
+    const size_t chunks = total >> 3;
+    uint4 *out4 = reinterpret_cast<uint4 *>(out);
+    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < chunks; q += (size_t)gridDim.x * blockDim.x) {
+        const size_t e0 = q << 3;
+        size_t m;
+        int c0;
+        if (total <= 0xffffffffull) {
+            const uint32_t mm = (uint32_t)e0 / (uint32_t)c_n;
+            m = mm;
+            c0 = (int)((uint32_t)e0 - mm * (uint32_t)c_n);
         } else {
-            out[e0] = (uint16_t)v;
+            m = e0 / (size_t)c_n;
+            c0 = (int)(e0 - m * (size_t)c_n);
+        }
+        uint32_t bits = obs_remap<IDENT>(words[m], t, c_n) >> c0;
+        for (int have = c_n - c0; have < 8; have += c_n) {
+            m++;  // (m < m_words: the chunk lies entirely inside the output)
+            bits |= obs_remap<IDENT>(words[m], t, c_n) << have;
+        }
+        uint4 v;
+        v.x = (bits & 1u) | ((bits << 15) & 0x10000u);
+        v.y = ((bits >> 2) & 1u) | ((bits << 13) & 0x10000u);
+        v.z = ((bits >> 4) & 1u) | ((bits << 11) & 0x10000u);
+        v.w = ((bits >> 6) & 1u) | ((bits << 9) & 0x10000u);
+        out4[q] = v;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {  // the last total % 8 elements
+        for (size_t e = chunks << 3; e < total; e++) {
+            const size_t m = e / (size_t)c_n;
+            out[e] = (uint16_t)((words[m] >> t.ch[e - m * (size_t)c_n]) & 1u);
         }
     }
 }

@@ -75,6 +75,7 @@ class SafeLifeEnv(object):
         self._seed = 0
         self._lib = _lib.load()
         self._steppers = {}
+        self._obs_scratch = False
         self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
         dev = self.pool.device
         self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
@@ -122,17 +123,26 @@ class SafeLifeEnv(object):
         """uint16 [N,vh,vw,C] (output_channels) or [N,vh,vw] (output_channels None)."""
         g = self.game
         vh, vw = self.view_shape
-        words = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=self.pool.device)
-        with torch.cuda.device(self.pool.device):
+        dev = self.pool.device
+        if torch.cuda.current_device() != self._dev_index:
+            torch.cuda.set_device(self._dev_index)
+        st = _lib.current_stream()
+        if not self.output_channels:
+            words = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=dev)
             _lib.check(self._lib.slb_get_obs(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
                                              g.state.data_ptr(), vh, vw, int(self.remove_white_goals),
-                                             words.data_ptr(), _lib.current_stream()))
-            if not self.output_channels:
-                return words
-            ch = self._channels()
-            out = torch.empty((g.n, vh, vw, ch.numel()), dtype=torch.uint16, device=self.pool.device)
-            _lib.check(self._lib.slb_obs_channels(words.data_ptr(), words.numel(), ch.data_ptr(),
-                                                  ch.numel(), out.data_ptr(), _lib.current_stream()))
+                                             words.data_ptr(), st))
+            return words
+        ch = self._channels()
+        out = torch.empty((g.n, vh, vw, ch.size), dtype=torch.uint16, device=dev)
+        scratch = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=dev) if self._obs_scratch else None
+        rc = self._lib.slb_get_obs_channels(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
+                                            g.state.data_ptr(), vh, vw, int(self.remove_white_goals),
+                                            ch.ctypes.data, ch.size, _lib.ptr(scratch), out.data_ptr(), st)
+        if rc == _lib.SLB_ERR_UNSUPPORTED and scratch is None:
+            self._obs_scratch = True  # this board / view shape takes the two-kernel path
+            return self.get_obs()
+        _lib.check(rc)
         return out
 
     def _channels(self):
@@ -140,7 +150,7 @@ class SafeLifeEnv(object):
         if getattr(self, "_ch_key", None) != key:
             if len(key) > 16 or any(c < 0 or c > 15 for c in key):
                 raise ValueError("output_channels must be at most 16 bit indices in 0..15")
-            self._ch = torch.tensor(list(key), dtype=torch.uint8, device=self.pool.device)
+            self._ch = np.array(key, dtype=np.uint8)  # host side: slb_obs_channels takes the list by value
             self._ch_key = key
         return self._ch
 

@@ -609,3 +609,43 @@ def test_out_of_band_writes_keep_the_step_exact(sl):
     st, ost = env2.game.state_numpy(), o2.states
     for f in st.dtype.names:
         assert (st[f] == ost[f]).all(), f
+
+
+@pytest.mark.parametrize("m,channels", [(1, (0,)), (7, tuple(range(15))), (225 * 3 + 1, tuple(range(15))),
+                                        (1001, (3, 0, 15, 9)), (64, tuple(range(16))), (333, (14, 2, 2, 7, 11, 0, 1)),
+                                        (5, (1, 2, 3))])
+def test_obs_channels_kernel(sl, m, channels):
+    """slb_obs_channels (safelife_env.py:152-154) for odd sizes, repeated / permuted channels."""
+    rng = np.random.RandomState(m)
+    words = rng.randint(0, 65536, size=m).astype(np.uint16)
+    w = torch.from_numpy(words).cuda()
+    ch = np.array(channels, dtype=np.uint8)
+    out = torch.full((m, len(channels)), 9, dtype=torch.uint16, device="cuda")
+    sl.lib.check(sl.lib.load().slb_obs_channels(w.data_ptr(), m, ch.ctypes.data, len(channels), out.data_ptr(),
+                                                sl.lib.current_stream()))
+    want = (words[:, None] >> ch[None, :].astype(np.uint16)) & 1
+    assert (out.cpu().numpy() == want).all()
+
+
+@pytest.mark.parametrize("h,w,view,channels", [(26, 26, (15, 15), tuple(range(15))), (26, 26, (33, 33), tuple(range(15))),
+                                               (9, 31, (7, 9), (0, 3, 9, 10, 11)), (32, 32, (5, 4), (15, 0, 1)),
+                                               (26, 26, (1, 1), (2,)), (40, 64, (15, 15), tuple(range(15))),
+                                               (40, 33, (9, 7), (1, 8, 9)), (26, 26, (35, 35), tuple(range(16)))])
+def test_fused_obs_equals_two_step(sl, h, w, view, channels):
+    """slb_get_obs_channels (one kernel on the warp-per-env shapes, 16-byte stores at 2-byte-aligned env
+    offsets) against slb_get_obs + the numpy channel split, on random mid-episode states."""
+    rng = np.random.RandomState(h + 7 * w + view[0])
+    lv = _random_levels(rng, 12, h, w)
+    n = 37
+    pool = sl.game.LevelPool(lv)
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, auto_reset=True, time_limit=25,
+                             view_shape=view, output_channels=channels)
+    env.seed(1)
+    env.reset()
+    for t in range(6):
+        obs, _, _, _ = env.step(rng.randint(9, size=n))
+        env.output_channels = None
+        words = env.get_obs().cpu().numpy()
+        env.output_channels = channels
+        want = (words[..., None] >> np.array(channels, np.uint16)) & 1
+        assert obs.shape == want.shape and (obs.cpu().numpy() == want).all(), t
