@@ -128,6 +128,11 @@ int slb_resident_import(const uint16_t *d_cells, void *d_res, int n, int h, int 
                         slb_pool *pool, int which, void *stream);
 int slb_resident_export(const void *d_res, uint16_t *d_cells, int n, int h, int w, void *stream);
 
+/* slb_pool is passed to the kernels BY VALUE at launch: a CUDA graph into which the caller captured one
+ * of the calls below must be captured again after anything that changes the struct (slb_pool_prepare,
+ * slb_resident_import with a pool, the single-stage calls that set external_writes).  Preparing a pool
+ * again invalidates the envs that play it until they are reset. */
+
 /* Fills pool->baseline (performance_ratio's baseline_score, safelife_game.py:622),
  * pool->exit_mask (update_exit_locs, :528-529), the resident copies of the levels, plane_bits and
  * (synchronising the stream once) plane_groups. */
@@ -206,7 +211,7 @@ int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       int auto_reset_stride, void *stream);
 
 /* The same without the final wait: H2D copy, step and D2H copy are queued on `stream` (give steps that
- * should overlap their own streams; at most 8 streams per calling thread).  h_actions is consumed
+ * should overlap their own streams; at most 8 streams with a step in flight per calling thread).  h_actions is consumed
  * before the call returns; h_reward / h_done are valid only after slb_stream_wait(stream), called from
  * the SAME host thread, returns (a plain cudaStreamSynchronize is not enough: on a non-default stream
  * the three operations run as one cached CUDA graph through a page-locked staging block inside the

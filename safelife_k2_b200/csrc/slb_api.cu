@@ -488,6 +488,7 @@ struct HostIo {
     StepGraph graphs[kGraphsPerSlot];
     int n_graphs;
     uint64_t clock;
+    uint64_t last_use;
     int32_t *pend_reward;  // outputs of the step in flight still to be copied out of `h`
     uint8_t *pend_done;
     int pend_n;
@@ -501,14 +502,31 @@ HostIo *find_slot(cudaStream_t st) {
     return nullptr;
 }
 
+void release_slot(HostIo *s) {
+    for (int k = 0; k < s->n_graphs; k++) cudaGraphExecDestroy(s->graphs[k].exec);
+    if (s->d) cudaFree(s->d);
+    if (s->h) cudaFreeHost(s->h);
+    memset(s, 0, sizeof(*s));
+}
+
 int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
     HostIo *s = find_slot(st);
     if (!s) {
-        if (g_slots_used == 8) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 8 streams per thread");
-        s = &g_slots[g_slots_used++];
+        if (g_slots_used < 8) {
+            s = &g_slots[g_slots_used++];
+        } else {
+            // all slots taken: recycle the one used longest ago that has no step in flight (streams come
+            // and go in a long-running process; a destroyed stream's slot is idle by construction)
+            for (int k = 0; k < 8; k++)
+                if (!g_slots[k].pend_n && (!s || g_slots[k].last_use < s->last_use)) s = &g_slots[k];
+            if (!s) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 8 streams with a step in flight on one thread");
+            release_slot(s);
+        }
         memset(s, 0, sizeof(*s));
         s->st = st;
     }
+    static thread_local uint64_t use_clock = 0;
+    s->last_use = ++use_clock;
     if (need > s->cap) {
         SLB_CUDA(cudaStreamSynchronize(st));
         for (int k = 0; k < s->n_graphs; k++) cudaGraphExecDestroy(s->graphs[k].exec);

@@ -649,3 +649,26 @@ def test_fused_obs_equals_two_step(sl, h, w, view, channels):
         env.output_channels = channels
         want = (words[..., None] >> np.array(channels, np.uint16)) & 1
         assert obs.shape == want.shape and (obs.cpu().numpy() == want).all(), t
+
+
+def test_step_host_many_streams(sl):
+    """More streams than staging slots per thread: idle slots are recycled, results stay right."""
+    lv = gu.levels("append-still")
+    pool = sl.game.LevelPool(lv)
+    n = 64
+    a = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False)
+    b = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False)
+    for e in (a, b):
+        e.seed(4); e.reset()
+    rng = np.random.RandomState(0)
+    r = np.zeros(n, np.int32); d = np.zeros(n, np.uint8)
+    streams = [torch.cuda.Stream() for _ in range(12)]
+    for t in range(36):
+        acts = rng.randint(9, size=n).astype(np.uint8)
+        st = streams[t % 12]
+        st.wait_stream(streams[(t - 1) % 12])
+        a.step_host(acts, r, d, sync=False, stream=st)
+        a.wait(st)
+        _, rb, db, _ = b.step(acts)
+        assert (r == rb.cpu().numpy()).all() and (d == db.cpu().numpy()).all(), t
+    assert (a.game.state == b.game.state).all() and (a.game.board == b.game.board).all()
