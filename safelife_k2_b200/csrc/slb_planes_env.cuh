@@ -151,28 +151,47 @@ __device__ __forceinline__ int action_planes(uint32_t P[16], const Geo &g, int &
 // ---------------------------------------------------------------------------------------------
 struct RowScore { int points, current, possible; };
 
+// f(a, b, c) for every bit position, f given by its truth table: bit (4a + 2b + c) of TT
+template <unsigned TT>
+__device__ __forceinline__ uint32_t lut3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(TT));
+    return r;
+}
+
 __device__ __forceinline__ RowScore score_planes(const uint32_t B[16], const uint32_t G[16],
                                                  const Geo &g) {
     const uint32_t c0 = B[9], c1 = B[10], c2 = B[11];  // cell colour bits r, g, b
     const uint32_t g0 = G[9], g1 = G[10], g2 = G[11];  // goal colour bits
-    // minterms: index = r + 2 g + 4 b  ->  k r g y b m c w
-    const uint32_t Ck = ~(c0 | c1 | c2), Cr = c0 & ~c1 & ~c2, Cg = ~c0 & c1 & ~c2, Cy = c0 & c1 & ~c2;
-    const uint32_t Cb = ~c0 & ~c1 & c2, Cm = c0 & ~c1 & c2, Cc = ~c0 & c1 & c2, Cw = c0 & c1 & c2;
-    const uint32_t Gk = ~(g0 | g1 | g2), Gr = g0 & ~g1 & ~g2, Gg = ~g0 & g1 & ~g2, Gy = g0 & g1 & ~g2;
-    const uint32_t Gb = ~g0 & ~g1 & g2, Gm = g0 & ~g1 & g2, Gc = ~g0 & g1 & g2, Gw = g0 & g1 & g2;
-    // point_table value classes
-    const uint32_t s5 = (Gg & Cg) | (Gb & Cb) | (Gm & Cm) | (Gc & Cc);
-    const uint32_t s3 = (Gr & Cr) | (Gg & Cc) | (Gy & Cy) | (Gm & Cr) |
-                        (Gb & (Ck | Cg | Cm | Cc | Cw)) | (Gc & (Ck | Cg | Cb | Cw));
-    const uint32_t sm1 = (Gk | Gw) & Cr;
-    const uint32_t sm3 = ((Gr | Gm) & (Ck | Cg | Cb | Cc | Cw)) | ((Gg | Gb | Gc) & Cr) | (Gy & Ck);
+    // Colour index = r + 2 g + 4 b: k 0, r 1, g 2, y 3, b 4, m 5, c 6, w 7.  Every value class of the
+    // point table is an OR over goal colours of (goal colour in a set) & (cell colour in a set); a
+    // set of colours is a function of three planes, i.e. ONE lop3 whose truth table is the set's
+    // bit mask (29 logic operations for all four classes).
+#define SLB_CELL_IN(mask) lut3<(mask)>(c2, c1, c0)
+#define SLB_GOAL_IN(mask) lut3<(mask)>(g2, g1, g0)
+    const uint32_t Ck = SLB_CELL_IN(0x01), Cr = SLB_CELL_IN(0x02), Cy = SLB_CELL_IN(0x08), Cc = SLB_CELL_IN(0x40);
+    const uint32_t Gkw = SLB_GOAL_IN(0x81);  // black or white
+    const uint32_t Grm = SLB_GOAL_IN(0x22);  // red or magenta
+    // +5: cell colour == goal colour and goal in {g, b, m, c}
+    const uint32_t ne = (c0 ^ g0) | (c1 ^ g1) | (c2 ^ g2);
+    const uint32_t s5 = ~ne & SLB_GOAL_IN(0x74);
+    // +3: (r|m, r) (g, c) (y, y) (b, {k g m c w}) (c, {k g b w})
+    const uint32_t Gy = SLB_GOAL_IN(0x08);
+    const uint32_t s3 = (Grm & Cr) | (SLB_GOAL_IN(0x04) & Cc) | (Gy & Cy) | (SLB_GOAL_IN(0x10) & SLB_CELL_IN(0xE5)) |
+                        (SLB_GOAL_IN(0x40) & SLB_CELL_IN(0x95));
+    // -1: (k|w, r)
+    const uint32_t sm1 = Gkw & Cr;
+    // -3: (r|m, {k g b c w}) (g|b|c, r) (y, k)
+    const uint32_t sm3 = (Grm & SLB_CELL_IN(0xD5)) | (SLB_GOAL_IN(0x54) & Cr) | (Gy & Ck);
+#undef SLB_CELL_IN
+#undef SLB_GOAL_IN
     const uint32_t a = B[0] & g.wmask;
     // mask of performance_ratio: alive and not (frozen and immovable) (:616-620)
     const uint32_t m = a & (~B[4] | B[2] | B[15]);
     RowScore r;
     r.points = 5 * __popc(a & s5) + 3 * __popc(a & s3) - __popc(a & sm1) - 3 * __popc(a & sm3);
     r.current = __popc(m & (s5 | s3)) - __popc(m & (sm1 | sm3));
-    r.possible = __popc(~(Gk | Gw) & g.wmask);  // goal colour neither black nor white
+    r.possible = __popc(~Gkw & g.wmask);  // goal colour neither black nor white
     return r;
 }
 
