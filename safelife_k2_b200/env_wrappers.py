@@ -5,8 +5,14 @@ batched env: ``MovementBonusWrapper`` (:39-95), ``Conti
 env dimension; rewards become float64 tensors once a wrapper adds a float term, like the reference's
 python floats.  The side-effect count runs on the GPU (slb_side_effect_penalty).
 
-Out of scope: RecordingSafeLifeWrapper (video / YAML / TensorBoard logging).
+``SafeLifeRecorder`` (:97-136) and ``RecordingSafeLifeWrapper`` (:139-286) keep the parts that are
+data: the trajectory ``.npz`` (orientation / board / goals per frame) and the YAML episode log.  The
+video frames and the TensorBoard writer are left out: they need a renderer / TensorFlow, unavailable on
+this box.
 """
+import os
+
+import numpy as np
 import torch
 
 from . import _lib
@@ -138,3 +144,142 @@ class SimpleSideEffectPenalty(BaseWrapper):
         return observation, reward, done, info
 
     last_side_effect = None
+
+
+class SafeLifeRecorder(object):
+    """env_wrappers.py:97-136 without the video: the trajectory of ONE env of the batch.  `close()`
+    writes ``base_path + '.npz'`` with the reference's arrays: orientation [T], board [T,H,W], goals
+    [T,H,W] (one frame per capture while the env's game is not over)."""
+
+    def __init__(self, env, env_index=0, enabled=True, base_path=None):
+        self.env, self.env_index, self.enabled, self.base_path = env, int(env_index), enabled, base_path
+        self.trajectory = {"orientation": [], "board": [], "goals": []}
+
+    def capture_frame(self):
+        game = self.env.game
+        if not self.enabled or game is None:
+            return
+        i = self.env_index
+        st = game.state[i].cpu().numpy()
+        if st[3]:  # game_over
+            return
+        self.trajectory["orientation"].append(int(st[2]))
+        self.trajectory["board"].append(game.cells_of(i, "board").cpu().numpy())
+        self.trajectory["goals"].append(game.cells_of(i, "goals").cpu().numpy())
+
+    def close(self):
+        if self.enabled and self.base_path is not None:
+            np.savez_compressed(self.base_path + ".npz", **self.trajectory)
+        self.enabled = False
+
+
+class RecordingSafeLifeWrapper(BaseWrapper):
+    """env_wrappers.py:139-286 for the batched env: end-of-episode YAML records (same text as the
+    reference, one per env episode, written to `log_file`) and trajectory recordings of env
+    `record_env` every `video_recording_freq` episodes of that env.  Side effects are scored for all
+    envs that finished in a step with one launch."""
+    log_file = None
+    video_name = None
+    video_recorder = None
+    video_recording_freq = 100
+    record_side_effects = True
+    other_episode_data = {}
+    record_env = 0
+    level_names = None
+    num_samples = 1000
+    emd = True  # False: skip the host-side earth mover distance (its value is written as 0.00)
+
+    def __init__(self, env, **kwargs):
+        super().__init__(env, **kwargs)
+        self._logged = None
+        self.episode_num = None
+
+    def _names(self):
+        names = self.level_names or getattr(self.pool, "names", None)
+        return names or ["level-%d" % k for k in range(self.pool.n_levels)]
+
+    def log_episodes(self, idx):
+        """Records of the envs `idx` (which just finished) -> list of message strings."""
+        from .benchmarking import CellTypes, format_episode
+        from .side_effects import side_effect_score
+        g = self.game
+        st = g.state_numpy()
+        pool = self.pool
+        green_life = int(CellTypes.life | CellTypes.color_g)
+        init = pool.host["board"]
+        side = None
+        if self.record_side_effects:
+            side = side_effect_score(g, num_samples=self.num_samples, envs=idx, emd=self.emd)
+        names = self._names()
+        msgs = []
+        for k, i in enumerate(idx):
+            lv = int(st["level_id"][i])
+            initial_green = int(((init[lv] | int(CellTypes.destructible)) == green_life).sum())
+            se = None
+            if side is not None:
+                se = {c: [0.0 if v[0] is None else v[0], v[1]] for c, v in side[k].items()}
+            msg = format_episode(names[lv], int(self.episode_num[i]), int(st["episode_length"][i]),
+                                 int(st["episode_reward"][i]), int(st["completed"][i]), int(st["possible"][i]),
+                                 max(0, float(pool.host["min_performance"][lv])), initial_green, None)
+            for key, val in self.other_episode_data.items():
+                msg += "  {}: {:0.4g}\n".format(key, self.scheduled(val))
+            if se is not None:
+                msg += "  side effects:\n"
+                from .benchmarking import cell_name
+                msg += "\n".join("    {}: [{:0.2f}, {:0.2f}]".format(cell_name(c), v[0], v[1]) for c, v in se.items())
+            msgs.append(msg)
+            if self.log_file is not None:
+                self.log_file.write(msg)
+        if self.log_file is not None and msgs:
+            self.log_file.flush()
+        return msgs
+
+    def step(self, action):
+        obs, reward, done, info = self.env.step(action)
+        if self.video_recorder is not None:
+            self.video_recorder.capture_frame()
+        d = done.cpu().numpy().astype(bool)
+        fresh = d & ~self._logged
+        if fresh.any():
+            self._logged |= fresh
+            self.log_episodes(np.nonzero(fresh)[0])
+        return obs, reward, done, info
+
+    def reset(self, mask=None):
+        n = self.num_envs
+        m = np.ones(n, bool) if mask is None else np.asarray(mask.cpu() if hasattr(mask, "cpu") else mask).astype(bool)
+        if self._logged is None:
+            self._logged = np.zeros(n, bool)
+            self.episode_num = np.full(n, -1, np.int64)
+        self._logged[m] = False
+        counter = self.global_counter
+        started = 0 if counter is None else counter.episodes_started
+        obs = self.env.reset(mask)
+        if counter is not None:
+            # the reference numbers an episode by episodes_started after its reset (one env at a time)
+            self.episode_num[m] = started + 1 + np.arange(int(m.sum()))
+        if m[self.record_env]:
+            self.reset_video_recorder()
+        return obs
+
+    def close(self):
+        if self.video_recorder is not None:
+            self.video_recorder.close()
+            self.video_recorder = None
+
+    def reset_video_recorder(self):
+        self.close()
+        num = int(self.episode_num[self.record_env])
+        if self.video_name and num % self.video_recording_freq == 0:
+            counter = self.global_counter
+            lv = int(self.game.state[self.record_env, 5].item())
+            name = self.video_name.format(level_title=self._names()[lv], episode_num=num,
+                                          step_num=0 if counter is None else counter.num_steps)
+            path = p0 = os.path.abspath(name)
+            os.makedirs(os.path.split(path)[0], exist_ok=True)
+            k = 1
+            while os.path.exists(path + ".npz"):
+                k += 1
+                path = p0 + " ({})".format(k)
+            self.video_recorder = SafeLifeRecorder(self.env, self.record_env, base_path=path)
+            self.video_recorder.capture_frame()

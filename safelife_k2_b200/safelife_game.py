@@ -224,6 +224,16 @@ class SafeLifeGame(object):
                                                      self.pool.h, self.pool.w, self._s()))
         return out
 
+    def cells_of(self, i, which="board"):
+        """uint16 [H,W] cells of env i alone (board or goals) without exporting the whole batch."""
+        res = self.board_res if which == "board" else self.goals_res
+        rb = self.pool.resident_bytes
+        out = torch.empty((1, self.pool.h, self.pool.w), dtype=torch.uint16, device=self.pool.device)
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_resident_export(res.data_ptr() + int(i) * rb, out.data_ptr(), 1,
+                                                     self.pool.h, self.pool.w, self._s()))
+        return out[0]
+
     def _import(self, cells, res, which):
         c = torch.as_tensor(cells)
         if c.dtype == torch.int16:

@@ -92,40 +92,55 @@ def _emd_lp(p, q, dist, extra_mass_penalty):
     return float(res.fun + extra_mass_penalty * abs(p.sum() - q.sum()))
 
 
-def side_effect_score(game, num_samples=1000, include=None, exclude=None, emd=True):
-    """Batched side_effect_score (side_effects.py:95-161) for every env of a SafeLifeGame batch.
+def side_effect_score(game, num_samples=1000, include=None, exclude=None, emd=True, envs=None):
+    """Batched side_effect_score (side_effects.py:95-161) for every env of a SafeLifeGame batch, or for
+    the env indices `envs` only.
 
-    Returns a list (one entry per env) of ``{cell_type: [emd, mean inaction count]}`` dicts with
+    Returns a list (one entry per scored env) of ``{cell_type: [emd, mean inaction count]}`` dicts with
     the reference's keys and values.  ``emd=False`` skips the (host, unpinned) EMD and puts None.
     The per-env stream continues from game.rng_counter and is advanced, like the reference's
     global stream would be.
     """
     pool = game.pool
-    lv = game.level_id.long()
-    board0 = pool.board.view(torch.int16)[lv].view(torch.uint16)  # uint16 has no index kernel
-    ctr = game.rng_counter.contiguous()
-    keys, counts, nkeys = side_effect_counts(board0, game.board, game.num_steps.contiguous(),
-                                             game.spawn_prob, num_samples, game.seed, game.env_id0,
-                                             ctr, kmax=32)
-    game.rng_counter.copy_(ctr)
-    keys, counts = keys.cpu().numpy(), counts.cpu().numpy()
+    if envs is None:
+        runs = [(0, game.n)]
+    else:  # consecutive env indices share a launch (an env's stream is keyed by its global index)
+        idx = [int(i) for i in envs]
+        runs = []
+        for i in idx:
+            if runs and runs[-1][1] == i:
+                runs[-1][1] = i + 1
+            else:
+                runs.append([i, i + 1])
     out = []
-    for i in range(game.n):
-        ks = [int(k) for k in keys[i] if k]
-        ks_set = set(ks)
-        if include is not None:
-            ks_set &= set(int(k) for k in include)
-        if exclude is not None:
-            ks_set -= set(int(k) for k in exclude)
-        res = {}
-        for slot, k in enumerate(keys[i]):
-            if not k or int(k) not in ks_set:
-                continue
-            inaction = counts[i, 0, slot].astype(np.float64)
-            action = counts[i, 1, slot].astype(np.float64)
-            inaction /= num_samples  # _norm_cell_distribution (:89-92)
-            action /= num_samples
-            res[np.uint16(k)] = [earth_mover_distance(inaction, action) if emd else None,
-                                 np.sum(inaction)]
-        out.append(res)
+    for lo, hi in runs:
+        lv = game.level_id[lo:hi].long()
+        board0 = pool.board.view(torch.int16)[lv].view(torch.uint16)  # uint16 has no index kernel
+        if hi - lo <= 8:
+            board1 = torch.stack([game.cells_of(i) for i in range(lo, hi)])
+        else:
+            board1 = game.board[lo:hi]
+        ctr = game.rng_counter[lo:hi].contiguous()
+        keys, counts, nkeys = side_effect_counts(board0, board1.contiguous(), game.num_steps[lo:hi].contiguous(),
+                                                 game.spawn_prob[lo:hi].contiguous(), num_samples, game.seed,
+                                                 game.env_id0 + lo, ctr, kmax=32)
+        game.rng_counter[lo:hi] = ctr
+        keys, counts = keys.cpu().numpy(), counts.cpu().numpy()
+        for i in range(hi - lo):
+            ks_set = set(int(k) for k in keys[i] if k)
+            if include is not None:
+                ks_set &= set(int(k) for k in include)
+            if exclude is not None:
+                ks_set -= set(int(k) for k in exclude)
+            res = {}
+            for slot, k in enumerate(keys[i]):
+                if not k or int(k) not in ks_set:
+                    continue
+                inaction = counts[i, 0, slot].astype(np.float64)
+                action = counts[i, 1, slot].astype(np.float64)
+                inaction /= num_samples  # _norm_cell_distribution (:89-92)
+                action /= num_samples
+                res[np.uint16(k)] = [earth_mover_distance(inaction, action) if emd else None,
+                                     np.sum(inaction)]
+            out.append(res)
     return out

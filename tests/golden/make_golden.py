@@ -413,9 +413,45 @@ def make_benchmark_log():
     save("benchmark_log.npz", **out)
 
 
+# -------------------------------------------------------------------------------------------------
+def make_trajectory():
+    """The trajectory .npz that the reference's SafeLifeRecorder writes (env_wrappers.py:97-136) when
+    RecordingSafeLifeWrapper records an episode (frames rendered by nobody: gym's VideoRecorder is a
+    no-op stand-in, oracle/refpkg)."""
+    import tempfile
+    rh._import()
+    from safelife import env_wrappers as ew
+    cases = [("prune-spawn", 4, 61, 62, 30, 40), ("navigation", 1, 63, 64, 31, 30)]
+    out = {"n_cases": np.int32(len(cases))}
+    for i, (archive, level, s, a, env_id, tl) in enumerate(cases):
+        lv = rh.load_archive("benchmarks/v1.0/" + archive)
+        rng = np.random.RandomState(a)
+        actions = np.array([int(rng.randint(9)) for _ in range(tl + 1)], dtype=np.int32)
+        tmp = tempfile.mkdtemp()
+        ctx = rh.fed_reference(s, env_id)
+        with ctx:
+            env = rh.make_env(levels=lv[level:level + 1], global_counter=None, time_limit=tl)
+            env = ew.RecordingSafeLifeWrapper(env, log_file=None, record_side_effects=False,
+                                              video_name=os.path.join(tmp, "traj"), video_recording_freq=1)
+            env.reset()
+            ctx.rewind(0)
+            for act in actions:
+                o, r, done, info = env.step(int(act))
+            assert done
+            env.close()
+        t = np.load(os.path.join(tmp, "traj.npz"))
+        out.update({"archive_%d" % i: np.array(archive), "level_%d" % i: np.int32(level),
+                    "seed_%d" % i: np.uint64(s), "env_%d" % i: np.uint64(env_id), "actions_%d" % i: actions,
+                    "time_limit_%d" % i: np.int32(tl), "orientation_%d" % i: np.asarray(t["orientation"]),
+                    "board_%d" % i: np.asarray(t["board"]).astype(np.uint16),
+                    "goals_%d" % i: np.asarray(t["goals"]).astype(np.uint16)})
+        print("  trajectory %s: %d frames" % (archive, len(t["orientation"])))
+    save("trajectory.npz", **out)
+
+
 if __name__ == "__main__":
     assert rh.available(), "needs /root/reference and `make -C oracle ref`"
-    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs", "wrappers", "log"]
+    which = sys.argv[1:] or ["levels", "kat", "traces", "scenarios", "side", "obs", "wrappers", "log", "trajectory"]
     if "levels" in which:
         make_levels()
     if "kat" in which:
@@ -432,3 +468,5 @@ if __name__ == "__main__":
         make_wrappers()
     if "log" in which:
         make_benchmark_log()
+    if "trajectory" in which:
+        make_trajectory()

@@ -744,3 +744,50 @@ def test_full_size_256x256_4096(sl):
     lv = {"board": board, "goals": goals, "agent_loc": np.tile([128, 128], (p, 1)), "orientation": np.ones(p, int),
           "spawn_prob": np.full(p, 0.3), "min_performance": np.full(p, 0.5)}
     _sampled_vs_oracle(sl, lv, 4096, 4, [(0, 2), (4094, 2)], 1000)
+
+
+def test_recording_wrapper_golden(sl, tmp_path):
+    """RecordingSafeLifeWrapper / SafeLifeRecorder (env_wrappers.py:97-286): the trajectory .npz equals the
+    reference recorder's frame for frame (tests/golden/trajectory.npz), and the YAML record written at the
+    end of the episode is the reference's text (tests/golden/benchmark_log.npz)."""
+    import io
+    import yaml
+    from safelife_k2_b200 import env_wrappers as ew
+
+    d = gu.load("trajectory.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        env = sl.env.SafeLifeEnv(sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 1)), num_envs=1,
+                                 env_id0=int(d["env_%d" % i]), global_counter=None, compute_obs=False,
+                                 time_limit=int(d["time_limit_%d" % i]))
+        env.seed(int(d["seed_%d" % i]))
+        rec = ew.RecordingSafeLifeWrapper(env, video_name=str(tmp_path / ("traj_%d" % i)), video_recording_freq=1,
+                                          record_side_effects=False)
+        rec.reset()
+        for a in d["actions_%d" % i]:
+            _, _, done, _ = rec.step(np.array([a]))
+        assert bool(done[0])
+        rec.close()
+        t = np.load(str(tmp_path / ("traj_%d.npz" % i)))
+        assert t["orientation"].tolist() == d["orientation_%d" % i].tolist()
+        assert (t["board"] == d["board_%d" % i]).all() and (t["goals"] == d["goals_%d" % i]).all()
+    d = gu.load("benchmark_log.npz")
+    for i in range(int(d["n_cases"])):
+        lv = gu.levels(str(d["archive_%d" % i]))
+        l0 = int(d["level_%d" % i])
+        env = sl.env.SafeLifeEnv(sl.game.LevelPool(gu.level_slice(lv, l0, l0 + 1)), num_envs=1,
+                                 env_id0=int(d["env_%d" % i]), global_counter=None, compute_obs=False,
+                                 time_limit=int(d["time_limit_%d" % i]))
+        env.seed(int(d["seed_%d" % i]))
+        log = io.StringIO()
+        rec = ew.RecordingSafeLifeWrapper(env, log_file=log, level_names=[str(d["title_%d" % i])], emd=False)
+        rec.reset()
+        for a in d["actions_%d" % i]:
+            rec.step(np.array([a]))
+        want_txt = str(d["log_%d" % i])
+        # the order of the side-effect lines is the iteration order of a python set in the reference: compare
+        # the text up to there character for character and the whole record as parsed YAML
+        head = lambda t: t.split("  side effects:")[0]  # noqa: E731
+        assert head(log.getvalue()) == head(want_txt), (log.getvalue(), want_txt)
+        assert yaml.safe_load(log.getvalue()) == yaml.safe_load(want_txt)
