@@ -186,10 +186,12 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
-    actions += i;
-    if (reward_out) reward_out += i;
-    if (done_out) done_out += i;
-    int action = *actions;
+    // one-step launches bump the pointers once; the step loop indexes instead (fewer live registers)
+    int action = actions[i];
+    if (ONE) {
+        if (reward_out) reward_out += i;
+        if (done_out) done_out += i;
+    }
     load_res(bp, g, GB, B);
     load_res(gp, g, GG, G);
     LevelConsts lc = load_level(pool, e.level, g);
@@ -199,10 +201,7 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
 
     for (int t = 0; t < steps; t++) {
         int next_action = 0;
-        if (!ONE) {
-            actions += n;
-            if (t + 1 < steps) next_action = *actions;
-        }
+        if (!ONE && t + 1 < steps) next_action = actions[(size_t)(t + 1) * n + i];
         bool touched, life_touched, ch_b, ch_g = false;
         int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
                                    life_touched);
@@ -226,12 +225,9 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
         const int done = (e.ep_len > time_limit) || e.game_over;
         e.ep_done = done;
         if (lane == 0) {
-            if (reward_out) *reward_out = reward;
-            if (done_out) *done_out = (uint8_t)done;
-        }
-        if (!ONE) {
-            if (reward_out) reward_out += n;
-            if (done_out) done_out += n;
+            const size_t o = ONE ? 0 : (size_t)t * n + i;
+            if (reward_out) reward_out[o] = reward;
+            if (done_out) done_out[o] = (uint8_t)done;
         }
         if (done && auto_reset_stride > 0) {
             reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
