@@ -225,6 +225,35 @@ def run_b200(args):
     ms = distributed.max_over_ranks(ms, dev)
     clocks = sampler.summary()
 
+    # ---- informational: the same ring with even / odd batches on two streams (fork-join graph), so that
+    # one batch's load / drain overlaps the other's compute.  Not the headline: `value` stays single-stream.
+    overlap = None
+    if graph is not None:
+        s2 = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            graph2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph2, stream=side):
+                s2.wait_stream(side)
+                for i in range(ring):
+                    stream = side if i % 2 == 0 else s2
+                    step(i)
+                side.wait_stream(s2)
+        stream = torch.cuda.current_stream()
+        torch.cuda.synchronize()
+        graph2.replay()
+        torch.cuda.synchronize()
+        reps = max(1, min(n_replays, 2000))
+        o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        o0.record(stream)
+        for _ in range(reps):
+            graph2.replay()
+        o1.record(stream)
+        torch.cuda.synchronize()
+        oms = distributed.max_over_ranks(o0.elapsed_time(o1), dev) / (reps * ring)
+        overlap = {"streams": 2, "value": n * world / (oms * 1e-3), "ms_per_step": oms,
+                   "what": "same ring, even / odd batches on two streams inside one graph"}
+
     # ---- e2e: host-buffer steps through the public API (SafeLifeEnv.step_host -> slb_env_step_host*) ----
     # Every step copies that step's actions from pinned host memory to the device, runs the fused step
     # and copies reward + done back to pinned host memory.  Two independent env batches are kept in
@@ -295,6 +324,8 @@ def run_b200(args):
                 "serial_what": "one step at a time: copy in, step, copy out, wait"},
         "stats_allreduce": distributed.stats_dict(stats),
     }
+    if overlap is not None:
+        line["two_stream_overlap"] = overlap
     # CPU baseline on this box's host cores, bounded sample (rank 0, N=1 only)
     if world == 1 and not args.no_cpu:
         threads = len(os.sched_getaffinity(0))
