@@ -10,10 +10,10 @@ namespace slb {
 constexpr int SE_FAST_MAX_KEYS = 64;
 
 struct SideSmem {  // per-warp carve-up of dynamic shared memory (in 32-bit words)
-    int kmax, nplanes;
+    int kcap, nplanes;  // kcap: number of cell types the shared counters have room for
     __host__ __device__ size_t words() const {
-        return (size_t)2 * kmax * nplanes * 32  // counters [branch][key][plane][lane]
-               + (size_t)kmax * 16              // per-key plane selectors (0 / ~0)
+        return (size_t)2 * kcap * nplanes * 32  // counters [branch][key][plane][lane]
+               + (size_t)kcap * 16              // per-key plane selectors (0 / ~0)
                + 32 * 34 / 2;                   // uint16 staging area for load/store
     }
 };
@@ -78,17 +78,21 @@ __global__ void __launch_bounds__(128)
 side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__restrict__ board1, int n,
                         int h, int w, const int32_t *__restrict__ num_steps, int num_samples,
                         const float *__restrict__ spawn_prob, uint64_t seed, uint64_t env_id0,
-                        uint64_t *counters, int kmax, int nplanes, uint16_t *keys, uint16_t *counts,
-                        int32_t *nkeys_out, bool vec) {
+                        uint64_t *counters, int kmax, int kcap, int retry, int nplanes, uint16_t *keys,
+                        uint16_t *counts, int32_t *nkeys_out, bool vec) {
     extern __shared__ __align__(16) uint32_t se_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i = blockIdx.x * (blockDim.x >> 5) + warp;
     if (i >= n) return;
-    SideSmem lay{kmax, nplanes};
+    // kcap < kmax is the first pass: most episodes see a handful of cell types, and counters for a
+    // handful fit 4 warps per CTA and 2 CTAs per SM.  An episode that needs more reports -1 and leaves
+    // its draw counter alone; the retry pass (full capacity, few warps per SM) redoes only those.
+    if (retry && nkeys_out[i] != -1) return;
+    SideSmem lay{kcap, nplanes};
     uint32_t *base = se_smem + warp * lay.words();
     uint32_t *cnt = base;
-    uint32_t *sel = cnt + (size_t)2 * kmax * nplanes * 32;
-    uint16_t *stage = reinterpret_cast<uint16_t *>(sel + (size_t)kmax * 16);
+    uint32_t *sel = cnt + (size_t)2 * kcap * nplanes * 32;
+    uint16_t *stage = reinterpret_cast<uint16_t *>(sel + (size_t)kcap * 16);
     const Geo g = make_geo(h, w);
     const size_t cells = (size_t)h * w;
     uint32_t A[16], C[16];
@@ -105,8 +109,12 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
     for (int t = 0; t < num_samples && !overflow; t++) {  // :137-141, the inaction board draws first
         counter = physics_planes(A, g, thr, seed, env, counter, ch);
         counter = physics_planes(C, g, thr, seed, env, counter, ch);
-        se_accumulate_planes(A, g, 0, kmax, nplanes, nkeys, overflow, cnt, sel);
-        se_accumulate_planes(C, g, 1, kmax, nplanes, nkeys, overflow, cnt, sel);
+        se_accumulate_planes(A, g, 0, kcap, nplanes, nkeys, overflow, cnt, sel);
+        se_accumulate_planes(C, g, 1, kcap, nplanes, nkeys, overflow, cnt, sel);
+    }
+    if (overflow) {  // warp-uniform
+        if (lane == 0) nkeys_out[i] = -1;
+        return;
     }
     if (counters && lane == 0) counters[i] = counter;
     __syncwarp();
@@ -120,7 +128,7 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
         }
         keys[(size_t)i * kmax + k] = (uint16_t)key;
     }
-    if (lane == 0) nkeys_out[i] = overflow ? -1 : nkeys;
+    if (lane == 0) nkeys_out[i] = nkeys;
     // counters -> uint16 maps [2][kmax][H][W] (same transposition as planes -> cells)
     const bool vec_out = fast_vec_ok(h, w, counts, counts);
     for (int br = 0; br < 2; br++)
@@ -128,7 +136,7 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
             uint32_t V[16];
 #pragma unroll
             for (int p = 0; p < 16; p++)
-                V[p] = (p < nplanes) ? cnt[((size_t)(br * kmax + k) * nplanes + p) * 32 + lane] : 0u;
+                V[p] = (p < nplanes) ? cnt[((size_t)(br * kcap + k) * nplanes + p) * 32 + lane] : 0u;
             store_planes(counts + (((size_t)i * 2 + br) * kmax + k) * cells, stage, h, w, vec_out, V);
         }
 }
@@ -141,20 +149,31 @@ inline bool launch_side_effect_fast(const uint16_t *b0, const uint16_t *b1, int 
                                     cudaStream_t st) {
     int nplanes = 1;
     while ((1 << nplanes) <= num_samples) nplanes++;
-    SideSmem lay{kmax, nplanes};
-    size_t per_warp = lay.words() * 4;
-    if (per_warp % 16) return false;  // keep each warp's region 16-byte aligned
-    int warps = 4;
-    while (warps > 1 && warps * per_warp > smem_limit) warps >>= 1;
-    if (warps * per_warp > smem_limit) return false;
-    size_t bytes = warps * per_warp;
-    if (bytes > 48 * 1024)
-        cudaFuncSetAttribute(side_effect_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    int grid = (n + warps - 1) / warps;
-    side_effect_fast_kernel<<<grid, warps * 32, bytes, st>>>(b0, b1, n, h, w, num_steps, num_samples, p,
-                                                          seed, env0, ctr, kmax, nplanes, keys, counts,
-                                                          nkeys, fast_vec_ok(h, w, b0, b1));
-    return true;
+    const bool vec = fast_vec_ok(h, w, b0, b1);
+    auto pass = [&](int kcap, int retry) -> bool {
+        SideSmem lay{kcap, nplanes};
+        size_t per_warp = lay.words() * 4;
+        if (per_warp % 16) return false;  // keep each warp's region 16-byte aligned
+        int warps = 4;
+        while (warps > 1 && warps * per_warp > smem_limit) warps >>= 1;
+        if (warps * per_warp > smem_limit) return false;
+        size_t bytes = warps * per_warp;
+        if (bytes > 48 * 1024)
+            cudaFuncSetAttribute(side_effect_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        int grid = (n + warps - 1) / warps;
+        side_effect_fast_kernel<<<grid, warps * 32, bytes, st>>>(b0, b1, n, h, w, num_steps, num_samples, p, seed,
+                                                              env0, ctr, kmax, kcap, retry, nplanes, keys,
+                                                              counts, nkeys, vec);
+        return true;
+    };
+    const int kfirst = 8;
+    if (kmax <= kfirst) return pass(kmax, 0);
+    // make sure the full-capacity pass can run before committing to the two-pass scheme
+    {
+        SideSmem lay{kmax, nplanes};
+        if ((lay.words() * 4) % 16 || lay.words() * 4 > smem_limit) return false;
+    }
+    return pass(kfirst, 0) && pass(kmax, 1);
 }
 
 }  // namespace slb

@@ -791,3 +791,41 @@ def test_recording_wrapper_golden(sl, tmp_path):
         head = lambda t: t.split("  side effects:")[0]  # noqa: E731
         assert head(log.getvalue()) == head(want_txt), (log.getvalue(), want_txt)
         assert yaml.safe_load(log.getvalue()) == yaml.safe_load(want_txt)
+
+
+def test_side_effect_counts_many_cell_types(sl):
+    """slb_side_effect_counts vs the oracle on boards with 3..20 distinct cell types: episodes with more
+    than 8 types take the kernel's second (full-capacity) pass, the others must be left as the first pass
+    wrote them; draw counters continue exactly in both."""
+    rng = np.random.RandomState(12)
+    n, h, w = 24, 26, 26
+    walls = [16 | (c << 9) for c in range(8)]               # frozen, 8 colours
+    trees = [17 | (c << 9) for c in range(1, 8)]            # frozen life, 7 colours
+    life = [9 | (c << 9) for c in (1, 2, 4)]                # destructible life
+    crates = [32788, 32788 | 1024]
+    spawner = [1688]
+    types = walls + trees + life + crates + spawner
+    b0 = np.zeros((n, h, w), np.uint16)
+    for i in range(n):
+        k = 3 + (i * 17) % 18
+        pick = rng.choice(len(types), size=k, replace=False)
+        vals = np.array([0] * 6 + [types[p] for p in pick], np.uint16)
+        b0[i] = vals[rng.randint(len(vals), size=(h, w))]
+    b1 = b0.copy()
+    b1[:, 5:8, 5:8] = 1033  # the "agent" left a block of green life
+    steps = rng.randint(0, 30, size=n).astype(np.int32)
+    ctr0 = rng.randint(0, 1000, size=n).astype(np.int64)
+    ctr = torch.from_numpy(ctr0.copy()).cuda()
+    keys, counts, nkeys = sl.se.side_effect_counts(torch.from_numpy(b0).cuda(), torch.from_numpy(b1).cuda(),
+                                                   steps, np.full(n, 0.3, np.float32), num_samples=60, seed=5,
+                                                   env_id0=100, counters=ctr, kmax=32)
+    keys, counts, nkeys, ctr = keys.cpu().numpy(), counts.cpu().numpy(), nkeys.cpu().numpy(), ctr.cpu().numpy()
+    assert nkeys.max() > 8 and nkeys.min() <= 8  # both passes are exercised
+    for i in range(n):
+        ok, oc, octr = slo.side_effect_counts(b0[i], b1[i], steps[i], num_samples=60, spawn_prob=0.3, seed=5,
+                                              env=100 + i, counter=int(ctr0[i]), kmax=32)
+        assert nkeys[i] == len(ok) and ctr[i] == octr, i
+        mine = {int(k): counts[i, :, s] for s, k in enumerate(keys[i]) if k}
+        assert sorted(mine) == sorted(int(k) for k in ok), i
+        for s, k in enumerate(ok):
+            assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
