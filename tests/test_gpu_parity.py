@@ -718,8 +718,37 @@ def _sampled_vs_oracle(sl, lv, n, steps, blocks, time_limit, seed=3, check_state
 
 
 def test_full_size_prune_spawn_16384(sl):
-    """BASELINE config 3 at full size: 16 384 envs with spawners, sampled envs bit-exact vs the oracle."""
-    _sampled_vs_oracle(sl, gu.levels("prune-spawn"), 16384, 40, [(0, 16), (8191, 24), (16384 - 16, 16)], 30)
+    """BASELINE configs 3 and 4 at full size.  Config 3: 16 384 prune-spawn envs (stochastic spawners, one
+    counter-based stream per env) for 1000 steps with resets, 256 sampled envs bit-exact vs the oracle at
+    every step and in their final state.  Config 4: side-effect count maps (1000 samples) of all 16 384
+    final states in one call, sampled episodes equal to the oracle's maps, keys and draw counters."""
+    lv = gu.levels("prune-spawn")
+    env = _sampled_vs_oracle(sl, lv, 16384, 1000, [(0, 96), (8100, 64), (16384 - 96, 96)], 300)
+    g = env.game
+    n = g.n
+    board1 = g.board
+    st = g.state_numpy()
+    board0 = torch.from_numpy(lv["board"][st["level_id"]]).cuda()
+    ctr0 = st["rng_counter"].astype(np.int64)
+    ctr = torch.from_numpy(ctr0.copy()).cuda()
+    spawn = lv["spawn_prob"][st["level_id"]].astype(np.float32)
+    keys, counts, nkeys = sl.se.side_effect_counts(board0, board1, st["num_steps"].astype(np.int32), spawn,
+                                                   num_samples=1000, seed=3, env_id0=0, counters=ctr, kmax=32)
+    nk = nkeys.cpu().numpy()
+    assert (nk >= 1).all() and (nk <= 32).all()
+    b1 = board1.cpu().numpy()
+    ctr = ctr.cpu().numpy()
+    for i in list(range(0, 8)) + list(range(5000, 5008)) + list(range(n - 8, n)):
+        ok, oc, octr = slo.side_effect_counts(lv["board"][st["level_id"][i]], b1[i], int(st["num_steps"][i]),
+                                              num_samples=1000, spawn_prob=float(spawn[i]), seed=3, env=i,
+                                              counter=int(ctr0[i]), kmax=32)
+        ki = keys[i].cpu().numpy()
+        ci = counts[i].cpu().numpy()
+        assert nk[i] == len(ok) and ctr[i] == octr, i
+        mine = {int(k): ci[:, s] for s, k in enumerate(ki) if k}
+        assert sorted(mine) == sorted(int(k) for k in ok), i
+        for s, k in enumerate(ok):
+            assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
 
 
 def test_full_size_mixed_65536(sl):
