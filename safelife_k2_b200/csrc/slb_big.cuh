@@ -71,11 +71,6 @@ __device__ __forceinline__ void big_store(uint32_t *__restrict__ base, const Big
     if (groups & 8u) b4[3 * g.items + item] = make_uint4(P[7], P[12], P[13], P[14]);
 }
 
-// the nine words of source plane `s` around an item, neighbours aligned to the item's columns
-struct Nine {
-    uint32_t ul, um, ur, ml, mm, mr, dl, dm, dr;
-};
-
 // The shared snapshot is item-major: word k of item i at src[i * BIG_SRC + k] (BIG_SRC is odd, so
 // consecutive items hit different banks); the nine neighbour items are addressed once per item and
 // every source plane is an immediate offset from them.
@@ -94,41 +89,52 @@ __device__ __forceinline__ BigNbr big_nbr(const uint32_t *src, const BigGeo &g, 
     return nb;
 }
 
+// The 3x3 summaries of source plane K around an item.  The three rows are reduced FIRST, separately for
+// the left, own and right word (that is word-parallel and needs no alignment); only the reduced words
+// are then aligned to the item's columns, so a summary costs 2 or 4 funnel shifts instead of 6.
+
+// OR over the 3x3
 template <int K>
-__device__ __forceinline__ Nine gather9(const BigNbr &nb) {
-    Nine n;
-    uint32_t l, m, r;
-    l = nb.ul[K]; m = nb.um[K]; r = nb.ur[K];
-    n.ul = __funnelshift_l(l, m, 1); n.um = m; n.ur = __funnelshift_r(m, r, 1);
-    l = nb.ml[K]; m = nb.mm[K]; r = nb.mr[K];
-    n.ml = __funnelshift_l(l, m, 1); n.mm = m; n.mr = __funnelshift_r(m, r, 1);
-    l = nb.dl[K]; m = nb.dm[K]; r = nb.dr[K];
-    n.dl = __funnelshift_l(l, m, 1); n.dm = m; n.dr = __funnelshift_r(m, r, 1);
-    return n;
+__device__ __forceinline__ uint32_t nine_or(const BigNbr &nb) {
+    const uint32_t l = or3(nb.ul[K], nb.ml[K], nb.dl[K]);
+    const uint32_t m = or3(nb.um[K], nb.mm[K], nb.dm[K]);
+    const uint32_t r = or3(nb.ur[K], nb.mr[K], nb.dr[K]);
+    return or3(__funnelshift_l(l, m, 1), m, __funnelshift_r(m, r, 1));
 }
 
-__device__ __forceinline__ uint32_t nine_or(const Nine &n) {
-    return or3(or3(n.ul, n.um, n.ur), or3(n.ml, n.mm, n.mr), or3(n.dl, n.dm, n.dr));
+// per-column 3-row sums (s + 2 c), aligned: left neighbour column, own column, right neighbour column
+struct ColSums { uint32_t sl, sm, sr, cl, cm, cr; };
+
+template <int K>
+__device__ __forceinline__ ColSums col_sums(const BigNbr &nb) {
+    uint32_t u = nb.ul[K], m = nb.ml[K], d = nb.dl[K];
+    const uint32_t s_l = xor3(u, m, d), c_l = maj3(u, m, d);
+    u = nb.um[K]; m = nb.mm[K]; d = nb.dm[K];
+    const uint32_t s_m = xor3(u, m, d), c_m = maj3(u, m, d);
+    u = nb.ur[K]; m = nb.mr[K]; d = nb.dr[K];
+    const uint32_t s_r = xor3(u, m, d), c_r = maj3(u, m, d);
+    ColSums c;
+    c.sl = __funnelshift_l(s_l, s_m, 1); c.sm = s_m; c.sr = __funnelshift_r(s_m, s_r, 1);
+    c.cl = __funnelshift_l(c_l, c_m, 1); c.cm = c_m; c.cr = __funnelshift_r(c_m, c_r, 1);
+    return c;
 }
 
-// >= 2 of the nine
-__device__ __forceinline__ uint32_t nine_two(const Nine &n) {
-    const uint32_t su = xor3(n.ul, n.um, n.ur), cu = maj3(n.ul, n.um, n.ur);
-    const uint32_t sm = xor3(n.ml, n.mm, n.mr), cm = maj3(n.ml, n.mm, n.mr);
-    const uint32_t sd = xor3(n.dl, n.dm, n.dr), cd = maj3(n.dl, n.dm, n.dr);
-    return or3(cu, cm, cd) | maj3(su, sm, sd);
+// >= 2 of the nine: some column holds two, or two columns hold an odd number
+template <int K>
+__device__ __forceinline__ uint32_t nine_two(const BigNbr &nb) {
+    const ColSums c = col_sums<K>(nb);
+    return or3(c.cl, c.cm, c.cr) | maj3(c.sl, c.sm, c.sr);
 }
 
-// n == 3 / n == 4 of the nine (n = s + 2 c summed over the three rows)
-__device__ __forceinline__ void nine_count(const Nine &n, uint32_t &is3, uint32_t &is4) {
-    const uint32_t su = xor3(n.ul, n.um, n.ur), cu = maj3(n.ul, n.um, n.ur);
-    const uint32_t sm = xor3(n.ml, n.mm, n.mr), cm = maj3(n.ml, n.mm, n.mr);
-    const uint32_t sd = xor3(n.dl, n.dm, n.dr), cd = maj3(n.dl, n.dm, n.dr);
-    const uint32_t t0 = xor3(su, sm, sd), t1 = maj3(su, sm, sd);  // ones: t0 + 2 t1
-    const uint32_t u0 = xor3(cu, cm, cd), u1 = maj3(cu, cm, cd);  // twos: u0 + 2 u1
-    const uint32_t n1 = t1 ^ u0, k = t1 & u0, n2 = u1 ^ k;        // n = t0 + 2 n1 + 4 n2 + 8 (u1 & k)
-    is3 = t0 & n1 & ~n2;
-    is4 = ~t0 & ~n1 & n2;
+// n == 3 / n == 4 of the nine (the adder tree of physics_planes)
+template <int K>
+__device__ __forceinline__ void nine_count(const BigNbr &nb, uint32_t &is3, uint32_t &is4) {
+    const ColSums c = col_sums<K>(nb);
+    const uint32_t s0 = xor3(c.sl, c.sm, c.sr), c0 = maj3(c.sl, c.sm, c.sr);
+    const uint32_t s1 = xor3(c.cl, c.cm, c.cr), c1 = maj3(c.cl, c.cm, c.cr);
+    const uint32_t n1 = c0 ^ s1, k = c0 & s1, n2 = c1 ^ k;  // n = s0 + 2 n1 + 4 n2 (+ 8)
+    is3 = s0 & n1 & ~n2;
+    is4 = ~s0 & ~n1 & n2;  // n2 set implies the 8s bit (c1 & k) is clear
 }
 
 // CTA-wide exclusive prefix sum of one int per thread (thread order); total returned to all.
@@ -208,32 +214,32 @@ __device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsign
         big_load(planes, g, it, groups, P);
         const uint32_t a = P[0], fz = P[4];
         uint32_t is3, is4;
-        nine_count(gather9<0>(nb), is3, is4);
+        nine_count<0>(nb, is3, is4);
         const uint32_t die0 = a & ~(fz | is3 | is4);
         const uint32_t open0 = ~(a | fz);
         uint32_t PR = 0, IH = 0;
         if (rf & 1u) {
-            PR = nine_or(gather9<1>(nb));
-            IH = nine_or(gather9<2>(nb));
+            PR = nine_or<1>(nb);
+            IH = nine_or<2>(nb);
         }
         const uint32_t die = die0 & ~PR;
         const uint32_t open = open0 & ~IH;
         const uint32_t birth = open & is3;
         uint32_t elig = 0;
-        if (rf & 2u) elig = open & ~is3 & nine_or(gather9<3>(nb));
+        if (rf & 2u) elig = open & ~is3 & nine_or<3>(nb);
         if (any7) sm.elig[it] = elig;
         const uint32_t flip = die | birth;
         if (flip) {
             uint32_t nD = 0, nR = 0, nG = 0, nB = 0;
             if (birth) {
-                nD = birth & nine_two(gather9<4>(nb));
-                uint32_t tR = nine_two(gather9<5>(nb));
-                uint32_t tG = nine_two(gather9<6>(nb));
-                uint32_t tB = nine_two(gather9<7>(nb));
+                nD = birth & nine_two<4>(nb);
+                uint32_t tR = nine_two<5>(nb);
+                uint32_t tG = nine_two<6>(nb);
+                uint32_t tB = nine_two<7>(nb);
                 if (rf & 2u) {
-                    tR |= nine_or(gather9<8>(nb));
-                    tG |= nine_or(gather9<9>(nb));
-                    tB |= nine_or(gather9<10>(nb));
+                    tR |= nine_or<8>(nb);
+                    tG |= nine_or<9>(nb);
+                    tB |= nine_or<10>(nb);
                 }
                 nR = birth & tR; nG = birth & tG; nB = birth & tB;
             }
@@ -292,9 +298,9 @@ __device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsign
         int r, j;
         big_row_word(g, it, r, j);
         const BigNbr nb = big_nbr(sm.src, g, r, j);
-        const uint32_t tR = nine_two(gather9<5>(nb)) | nine_or(gather9<8>(nb));
-        const uint32_t tG = nine_two(gather9<6>(nb)) | nine_or(gather9<9>(nb));
-        const uint32_t tB = nine_two(gather9<7>(nb)) | nine_or(gather9<10>(nb));
+        const uint32_t tR = nine_two<5>(nb) | nine_or<8>(nb);
+        const uint32_t tG = nine_two<6>(nb) | nine_or<9>(nb);
+        const uint32_t tB = nine_two<7>(nb) | nine_or<10>(nb);
         uint32_t P[16];
         big_load(planes, g, it, groups, P);
         const uint32_t keep = ~spawn;  // spawned cells were dead: their residue bits are discarded
