@@ -462,12 +462,25 @@ res_export_kernel(const uint32_t *__restrict__ planes, uint16_t *cells, int n, i
 // The combined board is formed on the planes, transposed once into a per-warp shared image of
 // uint16 cells, and gathered from there (any view size, also views larger than the board).
 // ---------------------------------------------------------------------------------------------
+// python's a % m for the view arithmetic, where a lies within a few multiples of m around [0, m)
+// (agent position +- view extent): one conditional add / subtract; the integer division is the rare path
 __device__ __forceinline__ int pymod_w(int a, int m) {
-    int r = a % m;
-    return r < 0 ? r + m : r;
+    if (a < 0) a += m;
+    else if (a >= m) a -= m;
+    if ((unsigned)a >= (unsigned)m) {  // only views larger than the board get here
+        a %= m;
+        if (a < 0) a += m;
+    }
+    return a;
 }
 
 struct ObsChannels { uint8_t ch[16]; };
+
+// the low 8 bits of `bits` as eight uint16 values 0 / 1 (element j = bit j), one 16-byte store
+__device__ __forceinline__ uint4 spread8(uint32_t bits) {
+    const uint32_t u = (bits & 0xffu) * 0x8001u;  // bit j at position j and at position j + 15
+    return make_uint4(u & 0x00010001u, (u >> 2) & 0x00010001u, (u >> 4) & 0x00010001u, (u >> 6) & 0x00010001u);
+}
 
 template <bool IDENT>
 __device__ __forceinline__ uint32_t obs_remap(uint32_t w, const ObsChannels &t, int c_n) {
@@ -583,18 +596,18 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
         out[l] = (uint16_t)((o[m] >> (l - m * c_n)) & 1u);
     }
     uint4 *out4 = reinterpret_cast<uint4 *>(out + head);
+    // chunk q starts at element head + 8 q: (cell m, channel c0) advance by 256 elements per iteration
+    uint32_t m = (head + ((uint32_t)lane << 3)) / (uint32_t)c_n;
+    int c0 = (int)(head + ((uint32_t)lane << 3) - m * c_n);
+    const uint32_t dm = 256u / (uint32_t)c_n;
+    const int dc = (int)(256u - dm * c_n);
     for (uint32_t q = lane; q < chunks; q += 32) {
-        const uint32_t l = head + (q << 3);
-        uint32_t m = l / (uint32_t)c_n;
-        const int c0 = (int)(l - m * c_n);
-        uint32_t bits = (uint32_t)o[m] >> c0;
-        for (int have = c_n - c0; have < 8; have += c_n) bits |= (uint32_t)o[++m] << have;
-        uint4 v;
-        v.x = (bits & 1u) | ((bits << 15) & 0x10000u);
-        v.y = ((bits >> 2) & 1u) | ((bits << 13) & 0x10000u);
-        v.z = ((bits >> 4) & 1u) | ((bits << 11) & 0x10000u);
-        v.w = ((bits >> 6) & 1u) | ((bits << 9) & 0x10000u);
-        out4[q] = v;
+        uint32_t bits = (uint32_t)o[m] >> c0, mm = m;
+        for (int have = c_n - c0; have < 8; have += c_n) bits |= (uint32_t)o[++mm] << have;
+        out4[q] = spread8(bits);
+        m += dm;
+        c0 += dc;
+        if (c0 >= c_n) { c0 -= c_n; m++; }
     }
 }
 
@@ -626,12 +639,7 @@ obs_channels_kernel(const uint16_t *__restrict__ words, size_t m_words, ObsChann
             m++;  // (m < m_words: the chunk lies entirely inside the output)
             bits |= obs_remap<IDENT>(words[m], t, c_n) << have;
         }
-        uint4 v;
-        v.x = (bits & 1u) | ((bits << 15) & 0x10000u);
-        v.y = ((bits >> 2) & 1u) | ((bits << 13) & 0x10000u);
-        v.z = ((bits >> 4) & 1u) | ((bits << 11) & 0x10000u);
-        v.w = ((bits >> 6) & 1u) | ((bits << 9) & 0x10000u);
-        out4[q] = v;
+        out4[q] = spread8(bits);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // the last total % 8 elements
         for (size_t e = chunks << 3; e < total; e++) {

@@ -119,8 +119,9 @@ class SafeLifeEnv(object):
             self.global_counter.episodes_started += started
         return self.get_obs() if self.compute_obs else None
 
-    def get_obs(self):
-        """uint16 [N,vh,vw,C] (output_channels) or [N,vh,vw] (output_channels None)."""
+    def get_obs(self, out=None):
+        """uint16 [N,vh,vw,C] (output_channels) or [N,vh,vw] (output_channels None).  `out`: an
+        existing cuda tensor of that shape to fill instead of allocating a new one every call."""
         g = self.game
         vh, vw = self.view_shape
         dev = self.pool.device
@@ -128,20 +129,21 @@ class SafeLifeEnv(object):
             torch.cuda.set_device(self._dev_index)
         st = _lib.current_stream()
         if not self.output_channels:
-            words = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=dev)
+            words = out if out is not None else torch.empty((g.n, vh, vw), dtype=torch.uint16, device=dev)
             _lib.check(self._lib.slb_get_obs(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
                                              g.state.data_ptr(), vh, vw, int(self.remove_white_goals),
                                              words.data_ptr(), st))
             return words
         ch = self._channels()
-        out = torch.empty((g.n, vh, vw, ch.size), dtype=torch.uint16, device=dev)
+        if out is None:
+            out = torch.empty((g.n, vh, vw, ch.size), dtype=torch.uint16, device=dev)
         scratch = torch.empty((g.n, vh, vw), dtype=torch.uint16, device=dev) if self._obs_scratch else None
         rc = self._lib.slb_get_obs_channels(self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
                                             g.state.data_ptr(), vh, vw, int(self.remove_white_goals),
                                             ch.ctypes.data, ch.size, _lib.ptr(scratch), out.data_ptr(), st)
         if rc == _lib.SLB_ERR_UNSUPPORTED and scratch is None:
             self._obs_scratch = True  # this board / view shape takes the two-kernel path
-            return self.get_obs()
+            return self.get_obs(out)
         _lib.check(rc)
         return out
 
