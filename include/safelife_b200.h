@@ -268,7 +268,7 @@ int slb_side_effect_penalty(const slb_pool *pool, int n, const void *d_board, co
 
 /* get_obs with the channel split fused in (safelife_env.py:125-155 in one call): d_out uint16
  * [N, vh, vw, n_channels], 16-byte aligned; h_channels as for slb_obs_channels.  Boards of 4..32 rows /
- * columns with vh * vw <= 1104 run as ONE kernel; any other shape goes through slb_get_obs +
+ * columns with vh * vw <= 1089 (33 x 33) run as ONE kernel; any other shape goes through slb_get_obs +
  * slb_obs_channels and needs d_words_scratch (uint16 [N, vh, vw]; SLB_ERR_UNSUPPORTED if it is NULL). */
 int slb_get_obs_channels(const slb_pool *pool, int n, const void *d_board, const void *d_goals,
                          const slb_env_state *d_state, int vh, int vw, int remove_white_goals,

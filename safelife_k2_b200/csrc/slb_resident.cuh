@@ -492,7 +492,7 @@ __device__ __forceinline__ uint32_t obs_remap(uint32_t w, const ObsChannels &t, 
     return r;
 }
 
-constexpr int RES_VIEW_U16 = 1104;  // largest view the fused channel output stages (33 x 33 = 1089)
+constexpr int RES_VIEW_U16 = 1089;  // largest view the fused channel output stages (33 x 33)
 
 // Observation of safelife_env.py:125-155 for one env per warp.  c_n == 0: packed words, obs is
 // uint16 [N, vh, vw].  c_n > 0 (vh * vw <= RES_VIEW_U16): the channel split is fused in, obs is
@@ -503,7 +503,7 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
                const uint32_t *__restrict__ goals, const slb_env_state *__restrict__ state, int vh,
                int vw, int remove_white, ObsChannels tab, int c_n, uint16_t *obs) {
     __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
-    __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? RES_VIEW_U16 : 8];
+    __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? 1104 : 8];  // RES_VIEW_U16 + 1 cells, rows 16-byte aligned
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i = blockIdx.x * RES_WARPS + warp;
     if (i >= n) return;
@@ -547,16 +547,21 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
     const int V = vh * vw;
     // the view goes to global memory (packed words) or to shared memory in channel order
     uint16_t *o = CHANNELS ? view_sm[warp] : obs + (size_t)i * V;
-    int vy = 0, vx = lane;  // (vy, vx) of flat index k = lane, advanced by 32 per iteration
-    while (vx >= vw) { vx -= vw; vy++; }
-    int sy = pymod_w(y1 + vy, h), sx = pymod_w(x1 + vx, w);
-    for (int k = lane; k < V; k += 32) {
-        const uint32_t v = sm[sy * S + sx];
-        o[k] = CHANNELS ? (uint16_t)obs_remap<IDENT>(v, tab, c_n) : (uint16_t)v;
-        vx += 32;
-        while (vx >= vw) { vx -= vw; vy++; }
-        sy = pymod_w(y1 + vy, h);
-        sx = pymod_w(x1 + vx, w);
+    // lane = view column (blocks of 32 for wider views); source column once per block, source row
+    // stepped with a wrap per view row
+    for (int vx0 = 0; vx0 < vw; vx0 += 32) {
+        const int vx = vx0 + lane;
+        const int sx = pymod_w(x1 + vx, w);
+        int sy = pymod_w(y1, h);
+        uint16_t *orow = o + vx;
+        for (int vy = 0; vy < vh; vy++) {
+            if (vx < vw) {
+                const uint32_t v = sm[sy * S + sx];
+                *orow = CHANNELS ? (uint16_t)obs_remap<IDENT>(v, tab, c_n) : (uint16_t)v;
+            }
+            orow += vw;
+            if (++sy == h) sy = 0;
+        }
     }
     __syncwarp();
     // move_to_perimeter: every initial exit cell, raster order
@@ -596,12 +601,46 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
         out[l] = (uint16_t)((o[m] >> (l - m * c_n)) & 1u);
     }
     uint4 *out4 = reinterpret_cast<uint4 *>(out + head);
+    uint32_t q0 = 0;
+    if (IDENT && c_n == 15) {
+        // The default channels (bits 0..14 in order): 8 cells are exactly 120 elements = 15 chunks.  Phase 1:
+        // a lane takes the 8 cells of group gq (one 16-byte shared load) plus the next one, packs their
+        // 15-bit words into a 128-bit string, shifts it by `head` (chunks are aligned to global 16-byte
+        // boundaries, cells to the env's first element) and parks the 15 bytes in a 16-byte slot of the
+        // staging area (the cell image there is dead by now).  Phase 2: lanes take consecutive chunks —
+        // one byte each — so that the 16-byte global stores of a warp are contiguous.
+        const uint32_t groups = (T - head) / 120u;
+        uint4 *slots = reinterpret_cast<uint4 *>(sm);
+        __syncwarp();
+        for (uint32_t gq = lane; gq < groups; gq += 32) {
+            const uint4 wa = *reinterpret_cast<const uint4 *>(o + 8 * gq);
+            const uint32_t w0 = wa.x & 0xffffu, w1 = wa.x >> 16, w2 = wa.y & 0xffffu, w3 = wa.y >> 16;
+            const uint32_t w4 = wa.z & 0xffffu, w5 = wa.z >> 16, w6 = wa.w & 0xffffu, w7 = wa.w >> 16;
+            const uint32_t w8 = o[8 * gq + 8];
+            const uint32_t p0 = w0 | (w1 << 15) | (w2 << 30);
+            const uint32_t p1 = (w2 >> 2) | (w3 << 13) | (w4 << 28);
+            const uint32_t p2 = (w4 >> 4) | (w5 << 11) | (w6 << 26);
+            const uint32_t p3 = (w6 >> 6) | (w7 << 9) | (w8 << 24);
+            slots[gq] = make_uint4(__funnelshift_r(p0, p1, head), __funnelshift_r(p1, p2, head),
+                                   __funnelshift_r(p2, p3, head), p3 >> head);
+        }
+        __syncwarp();
+        q0 = 15u * groups;
+        const uint8_t *bytes = reinterpret_cast<const uint8_t *>(sm);
+        uint32_t gg = (uint32_t)lane / 15u, jj = (uint32_t)lane - 15u * gg;  // chunk q = 15 gg + jj
+        for (uint32_t q = lane; q < q0; q += 32) {
+            out4[q] = spread8(bytes[gg * 16 + jj]);
+            gg += 2; jj += 2;  // 32 = 2 * 15 + 2
+            if (jj >= 15) { jj -= 15; gg++; }
+        }
+    }
     // chunk q starts at element head + 8 q: (cell m, channel c0) advance by 256 elements per iteration
-    uint32_t m = (head + ((uint32_t)lane << 3)) / (uint32_t)c_n;
-    int c0 = (int)(head + ((uint32_t)lane << 3) - m * c_n);
+    const uint32_t l0 = head + ((q0 + (uint32_t)lane) << 3);
+    uint32_t m = l0 / (uint32_t)c_n;
+    int c0 = (int)(l0 - m * c_n);
     const uint32_t dm = 256u / (uint32_t)c_n;
     const int dc = (int)(256u - dm * c_n);
-    for (uint32_t q = lane; q < chunks; q += 32) {
+    for (uint32_t q = q0 + lane; q < chunks; q += 32) {
         uint32_t bits = (uint32_t)o[m] >> c0, mm = m;
         for (int have = c_n - c0; have < 8; have += c_n) bits |= (uint32_t)o[++mm] << have;
         out4[q] = spread8(bits);
