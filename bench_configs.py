@@ -95,7 +95,7 @@ def synth_256(rng5, rng6, p):
 
 def main():
     names = [a for a in sys.argv[1:] if not a.startswith("--")] or ["prune_spawn_16384", "mixed_65536", "rollout_k32",
-                                                                   "big_256", "side_effects", "obs"]
+                                                                   "big_256", "side_effects", "step_obs", "obs"]
     quick = "--quick" in sys.argv
     out = []
     if "prune_spawn_16384" in names:
@@ -163,6 +163,34 @@ def main():
         cu = n * (T + 2000) * 676
         out.append({"config": "side_effects", "episodes": n, "num_steps": T, "num_samples": 1000, "seconds": dt,
                     "episodes_per_s": n / dt, "cell_updates_per_s": cu / dt, "max_keys": int(nkeys.max())})
+    if "step_obs" in names:
+        # the policy-in-the-loop pair: fused step, then the observation for the next action, one ring pass as a
+        # CUDA graph (device time; the Python call path costs more than both kernels at this size)
+        pool = LevelPool(gu.levels("append-still"))
+        n = 4096
+        envs = ring_envs(pool, n)
+        acts = torch.from_numpy(np.random.RandomState(3).randint(9, size=(n,)).astype(np.uint8)).cuda()
+        obs = torch.empty((n, 15, 15, 15), dtype=torch.uint16, device="cuda")
+        ch = np.arange(15, dtype=np.uint8)
+        lib = _lib.load()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            st = side.cuda_stream
+            with torch.cuda.graph(graph, stream=side):
+                for e in envs:
+                    g = e.game
+                    _lib.check(lib.slb_env_step(pool.c, n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
+                                                g.state.data_ptr(), acts.data_ptr(), 1000, 0, g.env_id0,
+                                                e._reward.data_ptr(), e._done.data_ptr(), e._stride(), st))
+                    _lib.check(lib.slb_get_obs_channels(pool.c, n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
+                                                        g.state.data_ptr(), 15, 15, 1, ch.ctypes.data, 15, None,
+                                                        obs.data_ptr(), st))
+        torch.cuda.synchronize()
+        ms = timed(graph.replay, 20 if quick else 100) / len(envs)
+        out.append({"config": "step_obs", "envs": n, "ms_per_step_plus_obs": ms, "env_steps_per_s": n / ms * 1e3,
+                    "what": "slb_env_step + slb_get_obs_channels (15x15x15) per env batch, ring of %d batches" % len(envs)})
     if "obs" in names:
         pool = LevelPool(gu.levels("append-still"))
         n = 4096
