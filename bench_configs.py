@@ -187,10 +187,22 @@ def main():
                     _lib.check(lib.slb_get_obs_channels(pool.c, n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
                                                         g.state.data_ptr(), 15, 15, 1, ch.ctypes.data, 15, None,
                                                         obs.data_ptr(), st))
+        graph2 = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            st = side.cuda_stream
+            with torch.cuda.graph(graph2, stream=side):
+                for e in envs:
+                    g = e.game
+                    _lib.check(lib.slb_env_step_obs(pool.c, n, g.board_res.data_ptr(), g.goals_res.data_ptr(),
+                                                    g.state.data_ptr(), acts.data_ptr(), 1000, 0, g.env_id0,
+                                                    e._reward.data_ptr(), e._done.data_ptr(), e._stride(), 15, 15, 1,
+                                                    ch.ctypes.data, 15, obs.data_ptr(), st))
         torch.cuda.synchronize()
         ms = timed(graph.replay, 20 if quick else 100) / len(envs)
+        ms2 = timed(graph2.replay, 20 if quick else 100) / len(envs)
         out.append({"config": "step_obs", "envs": n, "ms_per_step_plus_obs": ms, "env_steps_per_s": n / ms * 1e3,
-                    "what": "slb_env_step + slb_get_obs_channels (15x15x15) per env batch, ring of %d batches" % len(envs)})
+                    "ms_fused_step_obs": ms2, "env_steps_per_s_fused": n / ms2 * 1e3,
+                    "what": "slb_env_step + slb_get_obs_channels (15x15x15) per env batch vs slb_env_step_obs, ring of %d batches" % len(envs)})
     if "obs" in names:
         pool = LevelPool(gu.levels("append-still"))
         n = 4096

@@ -275,6 +275,17 @@ int slb_get_obs_channels(const slb_pool *pool, int n, const void *d_board, const
                          const uint8_t *h_channels, int n_channels, uint16_t *d_words_scratch,
                          uint16_t *d_out, void *stream);
 
+/* SafeLifeEnv.step up to and including get_obs (safelife_env.py:157-186 + 125-155) in ONE launch, for boards
+ * of 4..32 rows / columns: slb_env_step, then the observation of the state it produced (of the new episode
+ * where an env was auto-reset).  n_channels = 0: packed words uint16 [N, vh, vw]; else the channel split
+ * uint16 [N, vh, vw, n_channels] (vh * vw <= 1089, d_obs 16-byte aligned).  Other shapes:
+ * SLB_ERR_UNSUPPORTED — call slb_env_step and slb_get_obs(_channels). */
+int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                     const uint8_t *d_actions, int time_limit, uint64_t seed, uint64_t env_id0,
+                     int32_t *d_reward, uint8_t *d_done, int auto_reset_stride, int vh, int vw,
+                     int remove_white_goals, const uint8_t *h_channels, int n_channels, uint16_t *d_obs,
+                     void *stream);
+
 /* The channel split of safelife_env.py:152-154 for M packed words: d_out [M, n_channels] uint16,
  * d_out[m, c] = (d_words[m] >> h_channels[c]) & 1.  h_channels: n_channels <= 16 bit indices in HOST
  * memory (read before the call returns); d_out 16-byte aligned. */

@@ -68,6 +68,7 @@ SYMBOLS = {
                                     _vp, _vp, _vp, _vp]),
     "slb_accumulate_stats": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
     "slb_get_obs": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "slb_env_step_obs": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
     "slb_get_obs_channels": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "slb_side_effect_penalty": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp]),
     "slb_obs_channels": (_i, [_vp, _sz, _vp, _i, _vp, _vp]),

@@ -864,6 +864,33 @@ int slb_get_obs_channels(const slb_pool *pool, int n, const void *d_board, const
     return slb_obs_channels(d_words_scratch, (size_t)n * vh * vw, h_channels, n_channels, d_out, stream);
 }
 
+int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                     const uint8_t *d_actions, int time_limit, uint64_t seed, uint64_t env_id0,
+                     int32_t *d_reward, uint8_t *d_done, int auto_reset_stride, int vh, int vw,
+                     int remove_white_goals, const uint8_t *h_channels, int n_channels, uint16_t *d_obs,
+                     void *stream) {
+    if (int rc = check_pool(pool)) return rc;
+    if (n < 0 || vh < 1 || vw < 1 || !d_board || !d_goals || !d_state || !d_actions || !d_obs)
+        return fail(SLB_ERR_INVALID, "slb_env_step_obs: bad arguments");
+    ObsArgs oa = {};
+    bool ident = true;
+    if (n_channels != 0) {
+        if (int rc = obs_table(h_channels, n_channels, &oa.tab, &ident)) return rc;
+        if ((uintptr_t)d_obs % 16) return fail(SLB_ERR_INVALID, "slb_env_step_obs: d_obs must be 16-byte aligned");
+    }
+    if (!fast_shape(pool->h, pool->w) || (n_channels != 0 && (long long)vh * vw > RES_VIEW_U16))
+        return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_obs: this board / view shape takes slb_env_step + slb_get_obs");
+    if ((uint64_t)n * 16u * (uint64_t)pool->h >= (1ull << 32))
+        return fail(SLB_ERR_UNSUPPORTED, "too many envs per launch (resident word offsets are 32-bit)");
+    if (n == 0) return SLB_OK;
+    oa.vh = vh; oa.vw = vw; oa.remove_white = remove_white_goals; oa.c_n = n_channels; oa.obs = d_obs;
+    SLB_CUDA(launch_res_env_step_obs(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions,
+                                     time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, oa, ident,
+                                     (cudaStream_t)stream));
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
 int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *h_channels, int n_channels,
                      uint16_t *d_out, void *stream) {
     if (!d_words || !d_out) return fail(SLB_ERR_INVALID, "slb_obs_channels: bad arguments");

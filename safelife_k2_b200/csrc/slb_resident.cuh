@@ -497,22 +497,15 @@ constexpr int RES_VIEW_U16 = 1089;  // largest view the fused channel output sta
 // Observation of safelife_env.py:125-155 for one env per warp.  c_n == 0: packed words, obs is
 // uint16 [N, vh, vw].  c_n > 0 (vh * vw <= RES_VIEW_U16): the channel split is fused in, obs is
 // uint16 [N, vh, vw, c_n] and is written with 16-byte stores (obs must be 16-byte aligned).
+// obs_emit: the part after the planes are in registers (O = board planes, overwritten; G = goals), shared
+// by the stand-alone kernel and the fused step + observation kernel.  x0, y0: agent; e0: this lane's row of
+// the level's initial exit cells; sm / view: the warp's staging areas.
 template <bool CHANNELS, bool IDENT>
-__global__ void __launch_bounds__(RES_WARPS * 32)
-res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
-               const uint32_t *__restrict__ goals, const slb_env_state *__restrict__ state, int vh,
-               int vw, int remove_white, ObsChannels tab, int c_n, uint16_t *obs) {
-    __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
-    __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? 1104 : 8];  // RES_VIEW_U16 + 1 cells, rows 16-byte aligned
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int i = blockIdx.x * RES_WARPS + warp;
-    if (i >= n) return;
-    const Geo g = make_geo(pool.h, pool.w);
+__device__ __forceinline__ void obs_emit(uint32_t O[16], const uint32_t G[16], const Geo &g, int i, int x0, int y0,
+                                         uint32_t e0, int vh, int vw, int remove_white, const ObsChannels &tab,
+                                         int c_n, uint16_t *obs, uint16_t *sm, uint16_t *view) {
+    const int lane = threadIdx.x & 31;
     const int h = g.h, w = g.w, S = row_stride(w);
-    const size_t words = resident_words(h);
-    uint32_t O[16], G[16];
-    load_res(board + i * words, g, pool.plane_groups[0], O);
-    load_res(goals + i * words, g, 3u, G);  // only the colour planes (groups 0/1) are needed
     {
         uint32_t cr = G[9], cg = G[10], cb = G[11];
         if (remove_white) {
@@ -530,7 +523,6 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
         O[14] = t ^ c2;
         O[15] ^= c;
     }
-    uint16_t *sm = stage[warp];
     {
         uint32_t x[16];
         planes_to_cells(O, x);
@@ -541,12 +533,10 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
             if (lane < h && 2 * j < w) row[j] = x[j];
         __syncwarp();
     }
-    const slb_env_state *st = state + i;
-    const int x0 = st->agent_x, y0 = st->agent_y, level = st->level_id;
     const int x1 = x0 - vw / 2, y1 = y0 - vh / 2;
     const int V = vh * vw;
     // the view goes to global memory (packed words) or to shared memory in channel order
-    uint16_t *o = CHANNELS ? view_sm[warp] : obs + (size_t)i * V;
+    uint16_t *o = CHANNELS ? view : obs + (size_t)i * V;
     // lane = view column (blocks of 32 for wider views); source column once per block, source row
     // stepped with a wrap per view row
     for (int vx0 = 0; vx0 < vw; vx0 += 32) {
@@ -565,7 +555,6 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
     }
     __syncwarp();
     // move_to_perimeter: every initial exit cell, raster order
-    const uint32_t e0 = g.row ? pool.exit_mask[(size_t)level * h + lane] : 0u;
     unsigned rows = __ballot_sync(FULL, e0 != 0u);
     while (rows) {
         const int y = __ffs(rows) - 1;
@@ -648,6 +637,143 @@ res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
         c0 += dc;
         if (c0 >= c_n) { c0 -= c_n; m++; }
     }
+}
+
+constexpr int RES_VIEW_ROW = 1104;  // RES_VIEW_U16 + 1 cells, rows 16-byte aligned
+
+template <bool CHANNELS, bool IDENT>
+__global__ void __launch_bounds__(RES_WARPS * 32)
+res_obs_kernel(slb_pool pool, int n, const uint32_t *__restrict__ board,
+               const uint32_t *__restrict__ goals, const slb_env_state *__restrict__ state, int vh,
+               int vw, int remove_white, ObsChannels tab, int c_n, uint16_t *obs) {
+    __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
+    __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? RES_VIEW_ROW : 8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + warp;
+    if (i >= n) return;
+    const Geo g = make_geo(pool.h, pool.w);
+    const size_t words = resident_words(g.h);
+    uint32_t O[16], G[16];
+    load_res(board + i * words, g, pool.plane_groups[0], O);
+    load_res(goals + i * words, g, 3u, G);  // only the colour planes (groups 0/1) are needed
+    const slb_env_state *st = state + i;
+    const int x0 = st->agent_x, y0 = st->agent_y, level = st->level_id;
+    const uint32_t e0 = g.row ? pool.exit_mask[(size_t)level * g.h + lane] : 0u;
+    obs_emit<CHANNELS, IDENT>(O, G, g, i, x0, y0, e0, vh, vw, remove_white, tab, c_n, obs, stage[warp],
+                              view_sm[CHANNELS ? warp : 0]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// The policy-in-the-loop pair in one launch: one env step (the ONE path of res_env_rollout_kernel)
+// followed by the observation of the state it produced (after an in-kernel auto-reset: of the new
+// episode), straight from the planes in registers.  Saves the second launch and the observation
+// kernel's reload of board and goals.
+// ---------------------------------------------------------------------------------------------
+struct ObsArgs {
+    int vh, vw, remove_white, c_n;
+    ObsChannels tab;
+    uint16_t *obs;
+};
+
+template <unsigned GB, unsigned GG, int HW, bool CHANNELS, bool IDENT>
+__global__ void __launch_bounds__(RES_WARPS * 32, 28 / RES_WARPS)
+res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
+                        const uint8_t *__restrict__ actions, int time_limit, uint64_t seed, uint64_t env_id0,
+                        int32_t *reward_out, uint8_t *done_out, int auto_reset_stride, int l2_prefetch,
+                        ObsArgs oa) {
+    __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
+    __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? RES_VIEW_ROW : 8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i = blockIdx.x * RES_WARPS + warp;
+    asm volatile("griddepcontrol.launch_dependents;");
+    if (i >= n) return;
+    const Geo g = make_geo(HW ? HW : pool.h, HW ? HW : pool.w);
+    const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);
+    uint32_t *bp = board + off, *gp = goals + off;
+    uint32_t B[16], G[16];
+    if (l2_prefetch) {
+        const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
+        if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)bp + lane * 128));
+        if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)gp + lane * 128));
+        if (lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(state + i));
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    EnvRegs e = load_env(state + i);
+    const int action = actions[i];
+    load_res(bp, g, GB, B);
+    load_res(gp, g, GG, G);
+    LevelConsts lc = load_level(pool, e.level, g);
+    const uint64_t env = env_id0 + (uint64_t)i;
+    bool touched, life_touched, ch_b, ch_g = false;
+    int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
+                               life_touched);
+    e.num_steps += 1;
+    e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch_b);
+    if (!(lc.flags & SLB_LEVEL_GOALS_STATIC))
+        e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch_g);
+    bool g_dirty = ch_g;
+    if (life_touched || ch_b || ch_g || pool.external_writes) {
+        const int pts = score_and_paint(B, G, g, lc, e, true);
+        reward += pts - e.old_points;
+        e.old_points = pts;
+    }
+    e.ep_len += 1;
+    e.ep_reward += reward;
+    const int done = (e.ep_len > time_limit) || e.game_over;
+    e.ep_done = done;
+    if (lane == 0) {
+        if (reward_out) reward_out[i] = reward;
+        if (done_out) done_out[i] = (uint8_t)done;
+    }
+    if (done && auto_reset_stride > 0) {
+        reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
+        g_dirty = true;
+    }
+    store_res(bp, g, GB, B);
+    if (g_dirty) store_res(gp, g, GG, G);
+    if (lane == 0) store_env(state + i, e);
+    obs_emit<CHANNELS, IDENT>(B, G, g, i, e.ax, e.ay, lc.e0, oa.vh, oa.vw, oa.remove_white, oa.tab, oa.c_n, oa.obs,
+                              stage[warp], view_sm[CHANNELS ? warp : 0]);
+}
+
+inline cudaError_t launch_res_env_step_obs(const slb_pool &pool, int n, uint32_t *board, uint32_t *goals,
+                                           slb_env_state *state, const uint8_t *actions, int time_limit,
+                                           uint64_t seed, uint64_t env0, int32_t *reward, uint8_t *done, int stride,
+                                           const ObsArgs &oa, bool ident, cudaStream_t st) {
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
+    static const bool pdl = []() { const char *v = getenv("SLB_PDL"); return !v || v[0] != '0'; }();
+    static const bool pf = []() { const char *v = getenv("SLB_L2_PREFETCH"); return !v || v[0] != '0'; }();
+    const int l2_prefetch = pdl && pf;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((n + RES_WARPS - 1) / RES_WARPS);
+    cfg.blockDim = dim3(RES_WARPS * 32);
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const bool chan = oa.c_n > 0;
+#define SLB_SO3(GBV, GGV, HWV, CH, ID)                                                                        \
+    return cudaLaunchKernelEx(&cfg, res_env_step_obs_kernel<GBV, GGV, HWV, CH, ID>, pool, n, board, goals,     \
+                              state, actions, time_limit, seed, env0, reward, done, stride, l2_prefetch, oa)
+#define SLB_SO2(GBV, GGV, HWV)                                                                                \
+    do {                                                                                                      \
+        if (!chan) SLB_SO3(GBV, GGV, HWV, false, true);                                                       \
+        else if (ident) SLB_SO3(GBV, GGV, HWV, true, true);                                                   \
+        else SLB_SO3(GBV, GGV, HWV, true, false);                                                             \
+    } while (0)
+#define SLB_SO(GBV, GGV)                                                                                      \
+    do {                                                                                                      \
+        if (pool.h == 26 && pool.w == 26) SLB_SO2(GBV, GGV, 26);                                              \
+        else SLB_SO2(GBV, GGV, 0);                                                                            \
+    } while (0)
+    if (!(gg & ~3u) && !(gb & ~7u)) SLB_SO(7u, 3u);
+    else if (!(gg & ~3u)) SLB_SO(15u, 3u);
+    else SLB_SO(15u, 15u);
+#undef SLB_SO3
+#undef SLB_SO2
+#undef SLB_SO
 }
 
 // packed observation words [M] -> boolean channels [M, C] uint16 (safelife_env.py:152-154):

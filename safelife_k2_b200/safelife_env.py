@@ -76,6 +76,7 @@ class SafeLifeEnv(object):
         self._lib = _lib.load()
         self._steppers = {}
         self._obs_scratch = False
+        self._fused_obs = True
         self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
         dev = self.pool.device
         self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
@@ -162,12 +163,30 @@ class SafeLifeEnv(object):
         g = self.game
         acts = g._actions(action)
         already = g._field("episode_completed").clone() if self.global_counter is not None else None
+        obs = None
         with torch.cuda.device(self.pool.device):
-            _lib.check(self._lib.slb_env_step(
-                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
-                self._done.data_ptr(), self._stride() if self.auto_reset else 0,
-                _lib.current_stream()))
+            stride = self._stride() if self.auto_reset else 0
+            if self.compute_obs and self._fused_obs:
+                # step and observation in one launch (slb_env_step_obs) where the shapes allow it
+                vh, vw = self.view_shape
+                ch = self._channels() if self.output_channels else None
+                shape = (g.n, vh, vw, ch.size) if ch is not None else (g.n, vh, vw)
+                obs = torch.empty(shape, dtype=torch.uint16, device=self.pool.device)
+                rc = self._lib.slb_env_step_obs(
+                    self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+                    acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
+                    self._done.data_ptr(), stride, vh, vw, int(self.remove_white_goals),
+                    ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0,
+                    obs.data_ptr(), _lib.current_stream())
+                if rc == _lib.SLB_ERR_UNSUPPORTED:
+                    self._fused_obs, obs = False, None
+                else:
+                    _lib.check(rc)
+            if obs is None:
+                _lib.check(self._lib.slb_env_step(
+                    self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+                    acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
+                    self._done.data_ptr(), stride, _lib.current_stream()))
         done = self._done != 0
         if self.global_counter is not None:
             fresh = already == 0
@@ -178,7 +197,9 @@ class SafeLifeEnv(object):
             "times_up": g._field("episode_length") > self.time_limit,
             "episode": {"length": g._field("episode_length"), "reward": g._field("episode_reward")},
         })
-        return (self.get_obs() if self.compute_obs else None), self._reward, done, info
+        if obs is None and self.compute_obs:
+            obs = self.get_obs()
+        return obs, self._reward, done, info
 
     def step_host(self, actions_host, reward_host, done_host, sync=True, stream=None):
         """Host-buffer step (slb_env_step_host): uint8 actions in host memory in, int32 rewards / uint8
