@@ -151,6 +151,38 @@ __device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, c
     // e.counter deliberately untouched: the stream keeps running across episodes
 }
 
+// One env step on the planes in registers (safelife_env.py:157-186): action, physics of board then
+// goals, reward, exit colours, counters, done.  Shared by the rollout kernel
+// and the fused step + observation kernel.  Returns the step's reward; `done` as the env reports it.
+template <unsigned GB, unsigned GG>
+__device__ __forceinline__ int env_step_once(const slb_pool &pool, const Geo &g, uint32_t B[16], uint32_t G[16],
+                                             LevelConsts &lc, EnvRegs &e, int action, uint64_t seed, uint64_t env,
+                                             int time_limit, bool &g_dirty, int &done) {
+    bool touched, life_touched, ch_b, ch_g = false;
+    int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
+                               life_touched);
+    // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
+    e.num_steps += 1;
+    e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch_b);
+    if (!(lc.flags & SLB_LEVEL_GOALS_STATIC))  // a static goals board is its own successor
+        e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch_g);
+    g_dirty |= ch_g;
+    // The score reads alive cells (their colour, frozen / movable bits) and goal colours.  When
+    // the action moved no living cell and neither board changed, points, completed, possible
+    // and can_exit are what they were, and the exit cells (frozen, never overwritten by an
+    // action) still carry the colour painted for that can_exit.
+    if (life_touched || ch_b || ch_g || pool.external_writes) {
+        const int pts = score_and_paint(B, G, g, lc, e, true);
+        reward += pts - e.old_points;
+        e.old_points = pts;
+    }
+    e.ep_len += 1;
+    e.ep_reward += reward;
+    done = (e.ep_len > time_limit) || e.game_over;
+    e.ep_done = done;
+    return reward;
+}
+
 // ---------------------------------------------------------------------------------------------
 // A12 fused: T env steps per launch (T = 1 with a policy in the loop); board + goals stay in
 // registers between steps.  grid = ceil(N / RES_WARPS).
@@ -202,28 +234,8 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
     for (int t = 0; t < steps; t++) {
         int next_action = 0;
         if (!ONE && t + 1 < steps) next_action = actions[(size_t)(t + 1) * n + i];
-        bool touched, life_touched, ch_b, ch_g = false;
-        int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
-                                   life_touched);
-        // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
-        e.num_steps += 1;
-        e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch_b);
-        if (!(lc.flags & SLB_LEVEL_GOALS_STATIC))  // a static goals board is its own successor
-            e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch_g);
-        g_dirty |= ch_g;
-        // The score reads alive cells (their colour, frozen / movable bits) and goal colours.  When
-        // the action moved no living cell and neither board changed, points, completed, possible
-        // and can_exit are what they were, and the exit cells (frozen, never overwritten by an
-        // action) still carry the colour painted for that can_exit.
-        if (life_touched || ch_b || ch_g || pool.external_writes) {
-            const int pts = score_and_paint(B, G, g, lc, e, true);
-            reward += pts - e.old_points;
-            e.old_points = pts;
-        }
-        e.ep_len += 1;
-        e.ep_reward += reward;
-        const int done = (e.ep_len > time_limit) || e.game_over;
-        e.ep_done = done;
+        int done;
+        const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done);
         if (lane == 0) {
             const size_t o = ONE ? 0 : (size_t)t * n + i;
             if (reward_out) reward_out[o] = reward;
@@ -704,23 +716,9 @@ res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, 
     load_res(gp, g, GG, G);
     LevelConsts lc = load_level(pool, e.level, g);
     const uint64_t env = env_id0 + (uint64_t)i;
-    bool touched, life_touched, ch_b, ch_g = false;
-    int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
-                               life_touched);
-    e.num_steps += 1;
-    e.counter = physics_planes(B, g, lc.spawn_prob, seed, env, e.counter, ch_b);
-    if (!(lc.flags & SLB_LEVEL_GOALS_STATIC))
-        e.counter = physics_planes(G, g, lc.spawn_prob, seed, env, e.counter, ch_g);
-    bool g_dirty = ch_g;
-    if (life_touched || ch_b || ch_g || pool.external_writes) {
-        const int pts = score_and_paint(B, G, g, lc, e, true);
-        reward += pts - e.old_points;
-        e.old_points = pts;
-    }
-    e.ep_len += 1;
-    e.ep_reward += reward;
-    const int done = (e.ep_len > time_limit) || e.game_over;
-    e.ep_done = done;
+    bool g_dirty = false;
+    int done;
+    const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done);
     if (lane == 0) {
         if (reward_out) reward_out[i] = reward;
         if (done_out) done_out[i] = (uint8_t)done;
