@@ -179,10 +179,20 @@ __device__ __forceinline__ uint32_t box_two(uint32_t src, const Geo &g) {
     return hi | maj3(from_left(f0, g), f0, from_right(f0, g));
 }
 
-__device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g, float spawn_prob,
-                                                   uint64_t seed, uint64_t env, uint64_t counter,
-                                                   bool &changed) {
-    changed = false;
+// The step is split into "compute what flips" and "apply it" so that a caller can still use the old
+// board between the two (the side-effect kernel counts a board once per run of identical states).
+struct PhysDelta {
+    uint32_t flip;               // cells that die or are born
+    uint32_t born, nD, nR, nG, nB;  // births and the destructible / colour bits they inherit
+};
+
+// `quiet` (warp-uniform): nothing can die or be born and there is no spawner — a fixed point that
+// consumes no draws, now and at every later step.
+__device__ __forceinline__ uint64_t physics_compute(const uint32_t P[16], const Geo &g, float spawn_prob,
+                                                    uint64_t seed, uint64_t env, uint64_t counter,
+                                                    PhysDelta &dl, bool &quiet) {
+    dl.flip = dl.born = dl.nD = dl.nR = dl.nG = dl.nB = 0;
+    quiet = false;
     const uint32_t a = P[0], fz = P[4], sp = P[7];
     // ---- alive count of the 3x3 (centre included): n = s0 + 2 n1 + 4 n2 (+ 8), n <= 9 ----
     uint32_t is3, is4;
@@ -200,7 +210,10 @@ __device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g,
     const uint32_t die0 = a & ~(fz | is3 | is4);       // dies unless preserved
     const uint32_t open0 = ~(a | fz) & g.wmask;        // dead and not frozen
     const uint32_t birth0 = open0 & is3;               // born unless inhibited
-    if (!__any_sync(FULL, (die0 | birth0 | sp) != 0)) return counter;  // fixed point, no spawner
+    if (!__any_sync(FULL, (die0 | birth0 | sp) != 0)) {  // fixed point, no spawner
+        quiet = true;
+        return counter;
+    }
     // ---- flag summaries: taken from every cell of the 3x3, alive or not ----
     uint32_t PR = 0, IH = 0;
     if (__any_sync(FULL, (P[5] | P[6]) != 0)) {
@@ -248,17 +261,30 @@ __device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g,
         }
         nR = born & tR; nG = born & tG; nB = born & tB;
     }
-    const uint32_t flip = die | born;
-    if (!__any_sync(FULL, flip != 0)) return counter;
-    changed = true;
-    const uint32_t keep = ~flip;
+    dl.flip = die | born;
+    dl.born = born; dl.nD = nD; dl.nR = nR; dl.nG = nG; dl.nB = nB;
+    return counter;
+}
+
+__device__ __forceinline__ void physics_apply(uint32_t P[16], const PhysDelta &dl) {
+    const uint32_t keep = ~dl.flip;
 #pragma unroll
     for (int b = 0; b < 16; b++) P[b] &= keep;  // killed cells lose everything; births discard residue
-    P[0] |= born;
-    P[3] |= nD;
-    P[9] |= nR;
-    P[10] |= nG;
-    P[11] |= nB;
+    P[0] |= dl.born;
+    P[3] |= dl.nD;
+    P[9] |= dl.nR;
+    P[10] |= dl.nG;
+    P[11] |= dl.nB;
+}
+
+__device__ __forceinline__ uint64_t physics_planes(uint32_t P[16], const Geo &g, float spawn_prob,
+                                                   uint64_t seed, uint64_t env, uint64_t counter,
+                                                   bool &changed) {
+    PhysDelta dl;
+    bool quiet;
+    counter = physics_compute(P, g, spawn_prob, seed, env, counter, dl, quiet);
+    changed = !quiet && __any_sync(FULL, dl.flip != 0);
+    if (changed) physics_apply(P, dl);
     return counter;
 }
 

@@ -858,3 +858,55 @@ def test_side_effect_counts_many_cell_types(sl):
         assert sorted(mine) == sorted(int(k) for k in ok), i
         for s, k in enumerate(ok):
             assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("h,w,num_samples", [(26, 26, 1000), (26, 26, 5), (8, 9, 300), (32, 32, 2500), (13, 26, 17),
+                                               (30, 31, 4100)])
+def test_side_effect_counts_runs_and_fixed_points(sl, h, w, num_samples):
+    """slb_side_effect_counts vs the oracle where the run-length / fixed-point shortcuts of the kernel
+    matter: boards that are still from the start, that settle after a while (during the catch-up or in
+    the middle of the samples), period-2 oscillators, boards with spawners (never quiet), on shapes
+    whose high counter planes live in the output slice (26x26, 32x32) and shapes where they do not."""
+    rng = np.random.RandomState(h * 100 + w + num_samples)
+    n = 40
+    b0 = np.zeros((n, h, w), np.uint16)
+    b1 = np.zeros((n, h, w), np.uint16)
+    for i in range(n):
+        kind = i % 5
+        # a few still lifes (blocks) of two colours and some walls / crates
+        for _ in range(3):
+            y, x = rng.randint(0, h - 2), rng.randint(0, w - 2)
+            b0[i, y:y + 2, x:x + 2] = 9 | (rng.choice([1, 2, 4]) << 9)
+        b0[i, rng.randint(h), rng.randint(w)] = 16
+        b0[i, rng.randint(h), rng.randint(w)] = 32788
+        b1[i] = b0[i]
+        if kind == 1:    # the agent left a blinker: period-2 forever (or a collision that settles)
+            y, x = rng.randint(1, h - 1), rng.randint(0, w - 3)
+            b1[i, y, x:x + 3] = 1033
+        elif kind == 2:  # random soup in the action board: changes for a while, usually settles
+            y, x = rng.randint(0, h - 4), rng.randint(0, w - 4)
+            b1[i, y:y + 4, x:x + 4] = np.where(rng.rand(4, 4) < 0.5, 1033, 0)
+        elif kind == 3:  # soup in the INITIAL board as well: settles during the catch-up or the samples
+            y, x = rng.randint(0, h - 4), rng.randint(0, w - 4)
+            b0[i, y:y + 4, x:x + 4] = np.where(rng.rand(4, 4) < 0.5, 521, 0)
+            b1[i] = b0[i]
+            b1[i, rng.randint(h), rng.randint(w)] = 0
+        elif kind == 4:  # a spawner: draws every step
+            b0[i, h // 2, w // 2] = 1688
+            b1[i, h // 2, w // 2] = 1688
+    steps = rng.randint(0, 40, size=n).astype(np.int32)
+    ctr0 = rng.randint(0, 1000, size=n).astype(np.int64)
+    ctr = torch.from_numpy(ctr0.copy()).cuda()
+    keys, counts, nkeys = sl.se.side_effect_counts(torch.from_numpy(b0).cuda(), torch.from_numpy(b1).cuda(),
+                                                   steps, np.full(n, 0.3, np.float32), num_samples=num_samples,
+                                                   seed=9, env_id0=500, counters=ctr, kmax=12)
+    keys, counts, nkeys, ctr = keys.cpu().numpy(), counts.cpu().numpy(), nkeys.cpu().numpy(), ctr.cpu().numpy()
+    for i in range(n):
+        ok, oc, octr = slo.side_effect_counts(b0[i], b1[i], steps[i], num_samples=num_samples, spawn_prob=0.3,
+                                              seed=9, env=500 + i, counter=int(ctr0[i]), kmax=12)
+        assert nkeys[i] == len(ok) and ctr[i] == octr, i
+        mine = {int(k): counts[i, :, s] for s, k in enumerate(keys[i]) if k}
+        assert sorted(mine) == sorted(int(k) for k in ok), i
+        for s, k in enumerate(ok):
+            assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
