@@ -154,15 +154,52 @@ def main():
         lvl = g.level_id.long()
         board0 = pool.board.view(torch.int16)[lvl].view(torch.uint16)
         board1 = g.board
+        def run():
+            return se.side_effect_counts(board0, board1, g.num_steps.contiguous(), g.spawn_prob, 1000,
+                                         g.seed, g.env_id0, None, kmax=16)
+
+        run()  # the first call pays for the allocation of the [N,2,16,H,W] count maps (709 MB)
         torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
-        keys, counts, nkeys = se.side_effect_counts(board0, board1, g.num_steps.contiguous(), g.spawn_prob, 1000,
-                                                    g.seed, g.env_id0, None, kmax=16)
+        e0.record()
+        keys, counts, nkeys = run()
+        e1.record()
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
+        wall = time.perf_counter() - t0
+        dt = e0.elapsed_time(e1) * 1e-3
         cu = n * (T + 2000) * 676
         out.append({"config": "side_effects", "episodes": n, "num_steps": T, "num_samples": 1000, "seconds": dt,
-                    "episodes_per_s": n / dt, "cell_updates_per_s": cu / dt, "max_keys": int(nkeys.max())})
+                    "wall_seconds": wall, "episodes_per_s": n / dt, "cell_updates_per_s": cu / dt,
+                    "max_keys": int(nkeys.max()),
+                    "what": "prune-spawn episodes (spawners: both boards change at every sample); device time of "
+                            "one slb_side_effect_counts call incl. zero-filling the outputs"})
+        # the same for episodes of a still archive: the inaction board is a fixed point from the start
+        lv2 = gu.levels("append-still")
+        pool2 = LevelPool(lv2)
+        env2 = SafeLifeEnv(pool2, num_envs=n, global_counter=None, compute_obs=False)
+        env2.seed(0)
+        env2.reset()
+        env2.rollout(acts)
+        g2 = env2.game
+        b0 = pool2.board.view(torch.int16)[g2.level_id.long()].view(torch.uint16)
+        b1 = g2.board
+
+        def run2():
+            return se.side_effect_counts(b0, b1, g2.num_steps.contiguous(), g2.spawn_prob, 1000, g2.seed,
+                                         g2.env_id0, None, kmax=16)
+
+        run2()
+        torch.cuda.synchronize()
+        e0.record()
+        run2()
+        e1.record()
+        torch.cuda.synchronize()
+        dt2 = e0.elapsed_time(e1) * 1e-3
+        out.append({"config": "side_effects_still", "episodes": n, "num_steps": T, "num_samples": 1000,
+                    "seconds": dt2, "episodes_per_s": n / dt2, "nominal_cell_updates_per_s": cu / dt2,
+                    "what": "append-still episodes after 100 random actions: runs of identical states are counted "
+                            "once, draw-free fixed points end the rollout"})
     if "step_obs" in names:
         # the policy-in-the-loop pair: fused step, then the observation for the next action, one ring pass as a
         # CUDA graph (device time; the Python call path costs more than both kernels at this size)

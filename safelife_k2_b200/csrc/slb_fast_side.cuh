@@ -38,6 +38,7 @@ struct SideCtr {  // where one episode's counters live
     uint16_t *counts;     // the episode's [2][kmax][cells] output slice (high planes while running)
     int kcap, kmax, lo, nplanes;
     bool split;
+    bool rare;  // a countable cell of the episode has a bit outside selector slots 0-7
     size_t cells;
     // high planes of (branch, key): the 4-byte aligned start of that key's output slice
     __device__ __forceinline__ uint32_t *hi(int br, int k) const {
@@ -52,6 +53,15 @@ struct SideCtr {  // where one episode's counters live
 // split mode, weight < 16, pending plane known to have room
 __device__ __forceinline__ void se_add_fast(uint32_t *c, uint32_t m, uint32_t w) {
     const uint32_t v0 = c[0], v1 = c[32], v2 = c[64], v3 = c[96], v4 = c[128];
+    if (w == 1u) {  // the usual case on a board that changes every step
+        uint32_t cy = v0 & m;
+        c[0] = v0 ^ m;
+        c[32] = v1 ^ cy; cy &= v1;
+        c[64] = v2 ^ cy; cy &= v2;
+        c[96] = v3 ^ cy; cy &= v3;
+        c[128] = v4 | cy;
+        return;
+    }
     const uint32_t x0 = (w & 1u) ? m : 0u, x1 = (w & 2u) ? m : 0u, x2 = (w & 4u) ? m : 0u, x3 = (w & 8u) ? m : 0u;
     uint32_t cy = v0 & x0;
     c[0] = v0 ^ x0;
@@ -60,6 +70,12 @@ __device__ __forceinline__ void se_add_fast(uint32_t *c, uint32_t m, uint32_t w)
     c[96] = v3 ^ x3 ^ cy; cy = maj3(v3, x3, cy);
     c[128] = v4 | cy;
 }
+
+// Selector slot -> cell bit.  Slots 0-7 hold the bits benchmark boards use after the masking of
+// _add_cell_distribution (alive, frozen, spawning, colours, pushable, pullable), slots 8-13 the rest;
+// the agent and destructible bits (slots 14, 15) never take part in a match.
+constexpr uint64_t SE_SLOT_BITS = 0x31EDC865F2BA9740ull;  // nibble s = cell bit of slot s
+__host__ __device__ __forceinline__ int se_slot_bit(int s) { return (int)((SE_SLOT_BITS >> (4 * s)) & 15u); }
 
 // ripple add of weight * m over `np` planes at c (stride 32 words), starting with carry `cy` and the
 // weight bits `wb`; stops once the weight's bits and the carries ran out.  Returns the carry out.
@@ -103,16 +119,13 @@ __device__ __forceinline__ void se_accumulate_planes(const uint32_t P[16], int b
                                                      uint32_t &wsum) {
     const int lane = threadIdx.x & 31;
     // unchanging = (cell & (frozen|destructible|movable)) == frozen  -> zeroed (:61-62);
-    // the destructible bit is dropped from every cell (:62); agent cells and zeros are skipped (:68-70)
+    // the destructible bit is dropped from every cell (:62); agent cells and zeros are skipped (:68-70).
+    // On the cells of `todo` the masked value equals the cell itself (minus destructible, agent clear),
+    // so keys are matched against the planes P directly.
     const uint32_t keepm = ~(P[4] & ~P[3] & ~P[2] & ~P[15]);
-    uint32_t Q[16];
-    uint32_t nz = 0;
-#pragma unroll
-    for (int b = 0; b < 16; b++) {
-        Q[b] = (b == 3) ? 0u : (P[b] & keepm);
-        nz |= Q[b];
-    }
-    uint32_t todo = nz & ~Q[1];  // cells still to be attributed to a key
+    const uint32_t nz = or3(or3(P[0], P[2], P[4]), or3(P[5], P[6], P[7]), or3(P[8], P[9], P[10])) |
+                        or3(or3(P[11], P[12], P[13]), P[14], P[15]);
+    uint32_t todo = nz & keepm & ~P[1];  // cells still to be attributed to a key
     if (!__any_sync(FULL, todo != 0)) return;
     const bool fast = sc.split && weight < 16;
     if (sc.split) {
@@ -132,9 +145,10 @@ __device__ __forceinline__ void se_accumulate_planes(const uint32_t P[16], int b
             const int x = __ffs(__shfl_sync(FULL, todo, src)) - 1;
             uint32_t v = 0;
 #pragma unroll
-            for (int b = 0; b < 16; b++) v |= ((Q[b] >> x) & 1u) << b;
+            for (int b = 0; b < 16; b++)
+                if (b != 1 && b != 3) v |= ((P[b] >> x) & 1u) << b;
             v = __shfl_sync(FULL, v, src);
-            if (lane < 16) sc.sel[k * 16 + lane] = ((v >> lane) & 1u) ? 0xffffffffu : 0u;
+            if (lane < 16) sc.sel[k * 16 + lane] = ((v >> se_slot_bit(lane)) & 1u) ? 0xffffffffu : 0u;
             for (int br = 0; br < 2; br++) {  // zero both branches' counters of the new key
                 uint32_t *lw = sc.low(br, k);
                 for (int p = 0; p < sc.lo; p++) lw[p * 32] = 0;
@@ -147,11 +161,12 @@ __device__ __forceinline__ void se_accumulate_planes(const uint32_t P[16], int b
             __syncwarp();
         }
         const uint4 *s4 = reinterpret_cast<const uint4 *>(sc.sel + k * 16);
-        uint32_t diff = 0;
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
-            uint4 s = s4[q];
-            diff |= (Q[4 * q] ^ s.x) | (Q[4 * q + 1] ^ s.y) | (Q[4 * q + 2] ^ s.z) | (Q[4 * q + 3] ^ s.w);
+        const uint4 sa = s4[0], sb = s4[1];
+        uint32_t diff = (P[0] ^ sa.x) | (P[4] ^ sa.y) | (P[7] ^ sa.z) | (P[9] ^ sa.w) |
+                        (P[10] ^ sb.x) | (P[11] ^ sb.y) | (P[2] ^ sb.z) | (P[15] ^ sb.w);
+        if (sc.rare) {  // some cell of the episode carries one of the other bits
+            const uint4 sc4 = s4[2], sd = s4[3];
+            diff |= (P[5] ^ sc4.x) | (P[6] ^ sc4.y) | (P[8] ^ sc4.z) | (P[12] ^ sc4.w) | (P[13] ^ sd.x) | (P[14] ^ sd.y);
         }
         const uint32_t m = todo & ~diff;
         todo &= diff;
@@ -199,6 +214,12 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
     uint32_t A[16], C[16];
     load_planes(board0 + i * cells, stage, h, w, vec, A);
     load_planes(board1 + i * cells, stage, h, w, vec, C);
+    {   // cells that _add_cell_distribution zeroes are frozen and stay as they are for good; the step
+        // creates alive / destructible / colour bits only: the other bits of countable cells never grow
+        const uint32_t ra = (A[5] | A[6] | A[8] | A[12] | A[13] | A[14]) & ~(A[4] & ~A[3] & ~A[2] & ~A[15]);
+        const uint32_t rc = (C[5] | C[6] | C[8] | C[12] | C[13] | C[14]) & ~(C[4] & ~C[3] & ~C[2] & ~C[15]);
+        sc.rare = __any_sync(FULL, (ra | rc) != 0);
+    }
     const uint64_t env = env_id0 + (uint64_t)i;
     const float thr = spawn_prob[i];
     uint64_t counter = counters ? counters[i] : 0;
@@ -260,7 +281,7 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
     for (int k = lane; k < kmax; k += 32) {
         uint32_t key = 0;
         if (k < nkeys) {
-            for (int b = 0; b < 16; b++) key |= (sc.sel[k * 16 + b] & 1u) << b;
+            for (int b = 0; b < 16; b++) key |= (sc.sel[k * 16 + b] & 1u) << se_slot_bit(b);
             uint32_t bt = key & ~(uint32_t)COLORS;
             if (bt == ALIVE || bt == (FROZEN | SPAWNING)) key |= DESTRUCTIBLE;
         }

@@ -228,7 +228,10 @@ __device__ __forceinline__ uint64_t physics_compute(const uint32_t P[16], const 
     if (any_sp) {
         const uint32_t elig = open & ~is3 & box_or(sp, g);  // the cells that consume a draw (:110)
         if (__any_sync(FULL, elig != 0)) {
-            // raster-order rank of every eligible cell: exclusive prefix over rows, then in the row
+            // raster-order rank of every eligible cell: exclusive prefix over rows, then in the row.
+            // The draw of rank r depends on r alone, so lane j evaluates the draws of ranks j, j + 32, ...
+            // (one Philox evaluation per 32 draws instead of one per eligible cell of the busiest row);
+            // a vote packs the 32 outcomes and every row picks the bits of its own ranks.
             const uint64_t thr = spawn_threshold(spawn_prob);
             int cnt = __popc(elig), incl = cnt;
             const int lane = threadIdx.x & 31;
@@ -237,15 +240,20 @@ __device__ __forceinline__ uint64_t physics_compute(const uint32_t P[16], const 
                 int t = __shfl_up_sync(FULL, incl, o);
                 if (lane >= o) incl += t;
             }
-            uint64_t base = counter + (uint64_t)(incl - cnt);
-            uint32_t e = elig;
-            while (e) {
-                uint32_t bit = e & (0u - e);
-                e ^= bit;
-                if (stream_u53(seed, env, base) < thr) spawn |= bit;
-                base++;
+            const int total = __shfl_sync(FULL, incl, 31);
+            for (int c0 = 0; c0 < total; c0 += 32) {  // warp-uniform
+                const bool hit = (c0 + lane < total) && stream_u53(seed, env, counter + (uint64_t)(c0 + lane)) < thr;
+                const uint32_t outcomes = __ballot_sync(FULL, hit);
+                uint32_t e = elig;
+                int r = incl - cnt - c0;  // rank of this row's first eligible cell, relative to the chunk
+                while (e) {
+                    const uint32_t bit = e & (0u - e);
+                    e ^= bit;
+                    if ((unsigned)r < 32u && ((outcomes >> r) & 1u)) spawn |= bit;
+                    r++;
+                }
             }
-            counter += (uint64_t)__shfl_sync(FULL, incl, 31);
+            counter += (uint64_t)total;
         }
     }
     const uint32_t born = birth | spawn;
