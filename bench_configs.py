@@ -9,6 +9,7 @@ judged line for config 2).  Prints one JSON line per configuration:
   big_256             config 5b: 4096 envs at 256x256 (synthetic levels of SURVEY §8(d)), k=1
   side_effects        config 4: side_effect_score counts (1000 samples) for finished prune-spawn episodes
   obs                 get_obs 15x15x15 for 4096 envs
+  int_peak            LOP3 / LOP3+IMAD issue-rate microbenchmark (denominator of the integer roofline)
 
     python bench_configs.py [names...] [--quick]
 """
@@ -95,7 +96,7 @@ def synth_256(rng5, rng6, p):
 
 def main():
     names = [a for a in sys.argv[1:] if not a.startswith("--")] or ["prune_spawn_16384", "mixed_65536", "rollout_k32",
-                                                                   "big_256", "side_effects", "step_obs", "obs"]
+                                                                   "big_256", "side_effects", "step_obs", "obs", "int_peak"]
     quick = "--quick" in sys.argv
     out = []
     if "prune_spawn_16384" in names:
@@ -249,6 +250,33 @@ def main():
         ms = timed(env.get_obs, 200)
         out.append({"config": "obs", "envs": n, "view": [15, 15, 15], "ms_per_call": ms, "obs_per_s": n / ms * 1e3,
                     "write_GBps": n * 15 * 15 * 15 * 2 / (ms * 1e-3) / 1e9})
+    if "int_peak" in names:
+        # the integer roofline's denominator, measured here: LOP3 chains on every scheduler
+        import ctypes
+        lib = _lib.load()
+        sink = torch.zeros(4, dtype=torch.int32, device="cuda")
+        res = {"config": "int_peak", "what": "148 x 8 CTAs x 256 threads, 8 independent chains per thread; "
+                                              "kind 0 = LOP3 (ALU pipe), kind 1 = LOP3 + IMAD alternating (ALU + FMA pipes)"}
+        sm_count = torch.cuda.get_device_properties(0).multi_processor_count
+        for kind, name in ((0, "lop3"), (1, "lop3_imad")):
+            wi = ctypes.c_uint64()
+            st = torch.cuda.current_stream().cuda_stream
+
+            def go():
+                _lib.check(lib.slb_microbench_int(kind, sm_count * 8, 8192, sink.data_ptr(), ctypes.byref(wi), st))
+
+            ms = timed(go, 10, warm=3)
+            res[name + "_warp_inst_per_s"] = wi.value / (ms * 1e-3)
+            res[name + "_ms"] = ms
+        try:
+            import subprocess
+            mhz = float(subprocess.run(["nvidia-smi", "-i", "0", "--query-gpu=clocks.sm", "--format=csv,noheader,nounits"],
+                                       capture_output=True, text=True).stdout.strip())
+            res["sm_mhz_after"] = mhz
+        except Exception:
+            pass
+        res["sm_count"] = sm_count
+        out.append(res)
     for o in out:
         print(json.dumps(o))
 

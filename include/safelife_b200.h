@@ -292,6 +292,14 @@ int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, 
 int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *h_channels, int n_channels,
                      uint16_t *d_out, void *stream);
 
+/* ---- measurement aid (the integer roofline is measured on the box, not assumed) ----
+ * Launches a kernel of `ctas` x 256 threads in which every thread issues `iters` x 8 independent
+ * dependent-chain integer instructions: kind 0 = LOP3 only (the ALU pipe the bit-sliced stencil runs on),
+ * kind 1 = LOP3 and IMAD alternating (ALU + FMA pipes, the issue-rate ceiling).  The caller times the
+ * launch with events; *h_warp_insts (host, may be NULL) receives the warp instructions it issues
+ * (ctas * 8 warps * iters * 8, loop overhead not counted). */
+int slb_microbench_int(int kind, int ctas, int iters, uint32_t *d_sink, uint64_t *h_warp_insts, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

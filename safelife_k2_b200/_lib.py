@@ -72,6 +72,7 @@ SYMBOLS = {
     "slb_get_obs_channels": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "slb_side_effect_penalty": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp]),
     "slb_obs_channels": (_i, [_vp, _sz, _vp, _i, _vp, _vp]),
+    "slb_microbench_int": (_i, [_i, _i, _i, _vp, C.POINTER(_u64), _vp]),
 }
 
 _lib = None

@@ -8,6 +8,7 @@
 #include "slb_fast.cuh"
 #include "slb_generic_env.cuh"
 #include "slb_big.cuh"
+#include "slb_microbench.cuh"
 
 using namespace slb;
 
@@ -761,6 +762,16 @@ int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, i
             d_board0, d_board1, h, w, d_num_steps, num_samples, d_spawn_prob, seed, env_id0,
             d_counters, kmax, d_keys, d_counts, d_nkeys, d_scratch);
     }
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_microbench_int(int kind, int ctas, int iters, uint32_t *d_sink, uint64_t *h_warp_insts, void *stream) {
+    if (ctas < 1 || iters < 1 || !d_sink || (kind != 0 && kind != 1))
+        return fail(SLB_ERR_INVALID, "slb_microbench_int: bad arguments");
+    if (kind == 0) slb::int_peak_kernel<0><<<ctas, 256, 0, (cudaStream_t)stream>>>(d_sink, iters);
+    else slb::int_peak_kernel<1><<<ctas, 256, 0, (cudaStream_t)stream>>>(d_sink, iters);
+    if (h_warp_insts) *h_warp_insts = (uint64_t)ctas * 8ull * (uint64_t)iters * 8ull;
     SLB_LAUNCHED();
     return SLB_OK;
 }

@@ -216,8 +216,9 @@ side_effect_fast_kernel(const uint16_t *__restrict__ board0, const uint16_t *__r
     load_planes(board1 + i * cells, stage, h, w, vec, C);
     {   // cells that _add_cell_distribution zeroes are frozen and stay as they are for good; the step
         // creates alive / destructible / colour bits only: the other bits of countable cells never grow
-        const uint32_t ra = (A[5] | A[6] | A[8] | A[12] | A[13] | A[14]) & ~(A[4] & ~A[3] & ~A[2] & ~A[15]);
-        const uint32_t rc = (C[5] | C[6] | C[8] | C[12] | C[13] | C[14]) & ~(C[4] & ~C[3] & ~C[2] & ~C[15]);
+        // (the player itself — frozen, preserving, inhibiting — is skipped by the count and never changes)
+        const uint32_t ra = (A[5] | A[6] | A[8] | A[12] | A[13] | A[14]) & ~(A[4] & ~A[3] & ~A[2] & ~A[15]) & ~(A[1] & A[4]);
+        const uint32_t rc = (C[5] | C[6] | C[8] | C[12] | C[13] | C[14]) & ~(C[4] & ~C[3] & ~C[2] & ~C[15]) & ~(C[1] & C[4]);
         sc.rare = __any_sync(FULL, (ra | rc) != 0);
     }
     const uint64_t env = env_id0 + (uint64_t)i;
