@@ -493,6 +493,8 @@ struct HostIo {
     int32_t *pend_reward;  // outputs of the step in flight still to be copied out of `h`
     uint8_t *pend_done;
     int pend_n;
+    volatile uint32_t *pend_flag;  // direct path: the host word the step's last CTA publishes `pend_seq` to
+    uint32_t pend_seq, seq;
 };
 thread_local HostIo g_slots[8] = {};
 thread_local int g_slots_used = 0;
@@ -537,6 +539,9 @@ int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
         s->d = s->h = nullptr; s->cap = 0;
         SLB_CUDA(cudaMalloc(&s->d, need));
         SLB_CUDA(cudaMallocHost(&s->h, need));
+        SLB_CUDA(cudaMemsetAsync(s->d, 0, need, st));  // the direct path keeps a ticket counter in the block
+        SLB_CUDA(cudaStreamSynchronize(st));
+        memset(s->h, 0, need);
         s->cap = need;
     }
     *out = s;
@@ -544,9 +549,25 @@ int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
 }
 
 int finish_pending(HostIo *s) {
-    cudaError_t q;  // spin on the stream instead of a blocking wait: a step takes a few microseconds
-    while ((q = cudaStreamQuery(s->st)) == cudaErrorNotReady) {}
-    if (q != cudaSuccess) return fail(SLB_ERR_CUDA, "stream wait: %s", cudaGetErrorString(q));
+    cudaError_t q;  // spin instead of a blocking wait: a step takes a few microseconds
+    if (s->pend_flag) {
+        // direct path: the step's last CTA wrote the outputs to `h` and then its sequence number; look at
+        // the stream only now and then (a failed launch would never publish)
+        for (unsigned spins = 0; *s->pend_flag != s->pend_seq; spins++) {
+            if ((spins & 0xfff) == 0xfff) {
+                q = cudaStreamQuery(s->st);
+                if (q != cudaSuccess && q != cudaErrorNotReady) {
+                    s->pend_flag = nullptr; s->pend_n = 0;
+                    return fail(SLB_ERR_CUDA, "stream wait: %s", cudaGetErrorString(q));
+                }
+            }
+        }
+        __atomic_thread_fence(__ATOMIC_ACQUIRE);
+        s->pend_flag = nullptr;
+    } else {
+        while ((q = cudaStreamQuery(s->st)) == cudaErrorNotReady) {}
+        if (q != cudaSuccess) return fail(SLB_ERR_CUDA, "stream wait: %s", cudaGetErrorString(q));
+    }
     if (s->pend_n) {
         if (s->pend_reward) memcpy(s->pend_reward, s->h, (size_t)4 * s->pend_n);
         if (s->pend_done) memcpy(s->pend_done, s->h + (size_t)4 * s->pend_n, (size_t)s->pend_n);
@@ -561,6 +582,12 @@ bool host_graphs_enabled() {
 }
 
 inline size_t io_off_act(int n) { return ((size_t)5 * n + 15) & ~(size_t)15; }
+inline size_t io_off_ctr(int n) { return (io_off_act(n) + (size_t)n + 15) & ~(size_t)15; }  // ticket counter / sequence word
+
+bool host_direct_enabled() {
+    static const bool on = []() { const char *v = getenv("SLB_HOST_DIRECT"); return !v || v[0] != '0'; }();
+    return on;
+}
 
 // capture {H2D actions, step, D2H reward+done} on the slot's stream and instantiate it
 int build_step_graph(HostIo *s, const StepKey &k, cudaGraphExec_t *exec) {
@@ -595,9 +622,9 @@ int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env
     if (n == 0) return SLB_OK;
     if (int rc = check_pool(pool)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t off_done = (size_t)4 * n, off_act = io_off_act(n);
+    const size_t off_done = (size_t)4 * n, off_act = io_off_act(n), off_ctr = io_off_ctr(n);
     HostIo *s = nullptr;
-    if (int rc = host_io_slot(st, off_act + (size_t)n, &s)) return rc;
+    if (int rc = host_io_slot(st, off_ctr + 16, &s)) return rc;
     if (s->pend_n)  // an earlier step on this stream was never waited for: deliver its outputs first
         if (int rc = finish_pending(s)) return rc;
     uint8_t *d_io = s->d;
@@ -607,6 +634,24 @@ int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         SLB_CUDA(cudaStreamIsCapturing(st, &cs));
         graphed = cs == cudaStreamCaptureStatusNone;
+    }
+    if (graphed && host_direct_enabled() && n <= HOST_STEP_MAX_ENVS && fast_shape(pool->h, pool->w)) {
+        // no DMA copy on either side: actions by value in the launch parameters, outputs written to the
+        // pinned mirror by the step's last CTA, which then publishes this step's sequence number
+        static thread_local ActBlock acts;
+        memcpy(acts.a, h_actions, (size_t)n);
+        HostTail ht;
+        ht.d_reward = (int32_t *)d_io; ht.d_done = d_io + off_done;
+        ht.counter = (unsigned *)(d_io + off_ctr);
+        ht.h_block = s->h; ht.h_seq = (uint32_t *)(s->h + off_ctr);
+        ht.seq = ++s->seq;
+        if (ht.seq == 0) ht.seq = ++s->seq;  // 0 is the freshly allocated block's value
+        launch_res_env_step_host(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, acts, time_limit,
+                                 seed, env_id0, auto_reset_stride, ht, st);
+        SLB_LAUNCHED();
+        s->pend_reward = h_reward; s->pend_done = h_done; s->pend_n = n;
+        s->pend_flag = (volatile uint32_t *)ht.h_seq; s->pend_seq = ht.seq;
+        return SLB_OK;
     }
     if (!graphed) {
         SLB_CUDA(cudaMemcpyAsync(d_io + off_act, h_actions, (size_t)n, cudaMemcpyHostToDevice, st));
@@ -695,6 +740,7 @@ struct slb_stepper {
     slb_env_state *state;
     uint64_t seed, env_id0;
     void *stream;
+    int device;  // current device at creation; made current again by every step (callers hop devices)
     StepGraph graph;
 };
 
@@ -704,8 +750,10 @@ int slb_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals
     if (int rc = check_pool(pool)) return rc;
     if (!out || n < 0 || !d_board || !d_goals || !d_state)
         return fail(SLB_ERR_INVALID, "slb_stepper_create: bad arguments");
+    int dev = 0;
+    SLB_CUDA(cudaGetDevice(&dev));
     slb_stepper *s = new slb_stepper{pool, n, time_limit, auto_reset_stride, d_board, d_goals, d_state,
-                                     seed, env_id0, stream, {}};
+                                     seed, env_id0, stream, dev, {}};
     memset(&s->graph, 0, sizeof(s->graph));
     *out = s;
     return SLB_OK;
@@ -713,6 +761,8 @@ int slb_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals
 
 int slb_stepper_step(slb_stepper *s, const uint8_t *h_actions, int32_t *h_reward, uint8_t *h_done) {
     if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
+    int dev = s->device;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev != s->device) SLB_CUDA(cudaSetDevice(s->device));
     return host_step(s->pool, s->n, s->board, s->goals, s->state, h_actions, s->time_limit, s->seed,
                      s->env_id0, h_reward, h_done, s->stride, s->stream, &s->graph);
 }

@@ -295,6 +295,102 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
 #undef SLB_ROLL
 }
 
+// ---------------------------------------------------------------------------------------------
+// The host-buffer step without a DMA copy on either side (slb_env_step_host*, n <= 4096): the actions
+// travel in the launch parameters (4 KB by value), the step writes reward / done to a device staging
+// block, and the last CTA to finish (ticket counter) copies the whole block to the caller's mapped
+// pinned mirror with 16-byte stores, fences system-wide and publishes the step's sequence number
+// there; the host waits on that word instead of on the stream.
+// ---------------------------------------------------------------------------------------------
+constexpr int HOST_STEP_MAX_ENVS = 4096;
+struct ActBlock {
+    uint8_t a[HOST_STEP_MAX_ENVS];
+};
+struct HostTail {
+    int32_t *d_reward;   // device staging [reward 4n | done n], 16-byte aligned, padded to 16
+    uint8_t *d_done;
+    unsigned *counter;   // device, zero between launches
+    uint8_t *h_block;    // mapped pinned host mirror of the staging block
+    uint32_t *h_seq;     // mapped pinned host word
+    uint32_t seq;
+};
+
+template <unsigned GB, unsigned GG, int HW>
+__global__ void __launch_bounds__(RES_WARPS * 32, 28 / RES_WARPS)
+res_env_step_host_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
+                         const __grid_constant__ ActBlock acts, int time_limit, uint64_t seed,
+                         uint64_t env_id0, int auto_reset_stride, HostTail ht) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    if (i < n) {
+        const Geo g = make_geo(HW ? HW : pool.h, HW ? HW : pool.w);
+        const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);
+        uint32_t *bp = board + off, *gp = goals + off;
+        uint32_t B[16], G[16];
+        EnvRegs e = load_env(state + i);
+        const int action = acts.a[i];
+        load_res(bp, g, GB, B);
+        load_res(gp, g, GG, G);
+        LevelConsts lc = load_level(pool, e.level, g);
+        const uint64_t env = env_id0 + (uint64_t)i;
+        bool g_dirty = false;
+        int done;
+        const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done);
+        if (lane == 0) {
+            ht.d_reward[i] = reward;
+            ht.d_done[i] = (uint8_t)done;
+        }
+        if (done && auto_reset_stride > 0) {
+            reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
+            g_dirty = true;
+        }
+        store_res(bp, g, GB, B);
+        if (g_dirty) store_res(gp, g, GG, G);
+        if (lane == 0) store_env(state + i, e);
+    }
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(ht.counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        const int nvec = (5 * n + 15) >> 4;
+        const uint4 *src = reinterpret_cast<const uint4 *>(ht.d_reward);
+        uint4 *dst = reinterpret_cast<uint4 *>(ht.h_block);
+        for (int j = threadIdx.x; j < nvec; j += blockDim.x) dst[j] = __ldcg(src + j);
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            *ht.counter = 0;
+            *reinterpret_cast<volatile uint32_t *>(ht.h_seq) = ht.seq;
+        }
+    }
+}
+
+inline void launch_res_env_step_host(const slb_pool &pool, int n, uint32_t *board, uint32_t *goals,
+                                     slb_env_state *state, const ActBlock &acts, int time_limit,
+                                     uint64_t seed, uint64_t env0, int stride, const HostTail &ht,
+                                     cudaStream_t st) {
+    const int grid = (n + RES_WARPS - 1) / RES_WARPS;
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
+#define SLB_HS2(GBV, GGV, HWV)                                                                          \
+    res_env_step_host_kernel<GBV, GGV, HWV><<<grid, RES_WARPS * 32, 0, st>>>(                           \
+        pool, n, board, goals, state, acts, time_limit, seed, env0, stride, ht)
+#define SLB_HS(GBV, GGV)                                                                                \
+    do {                                                                                                \
+        if (pool.h == 26 && pool.w == 26) SLB_HS2(GBV, GGV, 26);                                        \
+        else SLB_HS2(GBV, GGV, 0);                                                                      \
+    } while (0)
+    if (!(gg & ~3u) && !(gb & ~7u)) SLB_HS(7u, 3u);
+    else if (!(gg & ~3u)) SLB_HS(15u, 3u);
+    else SLB_HS(15u, 15u);
+#undef SLB_HS2
+#undef SLB_HS
+}
+
 // pool prepare, after the resident copies exist: which levels have goals that never change
 // (a fixed point of advance_board without spawners; safelife_game.py:657-660 advances goals too)
 __global__ void __launch_bounds__(RES_WARPS * 32)

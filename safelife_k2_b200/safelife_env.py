@@ -22,6 +22,25 @@ def _hptr(x):
     return x if isinstance(x, int) or x is None else _lib.ptr(x)
 
 
+class HostStepper(object):
+    """See SafeLifeEnv.host_stepper.  Keeps its env alive (the env owns the native stepper)."""
+    __slots__ = ("_env", "_sp", "_step", "_wait", "_dev")
+
+    def __init__(self, env, sp):
+        self._env, self._sp, self._dev = env, sp, env._dev_index
+        self._step, self._wait = env._lib.slb_stepper_step, env._lib.slb_stepper_wait
+
+    def step(self, actions_ptr, reward_ptr, done_ptr):
+        rc = self._step(self._sp, actions_ptr, reward_ptr, done_ptr)
+        if rc:
+            _lib.check(rc)
+
+    def wait(self):
+        rc = self._wait(self._sp)
+        if rc:
+            _lib.check(rc)
+
+
 class _Info(dict):
     """The step's info dict (safelife_env.py:176-186).  'board' and 'goals' are uint16 [N,H,W]
     tensors exported from the resident state when first asked for, not on every step."""
@@ -220,6 +239,20 @@ class SafeLifeEnv(object):
             rc = self._lib.slb_stepper_wait(sp)
         if rc:
             _lib.check(rc)
+
+    def host_stepper(self, stream=None):
+        """The host-buffer step bound to this env batch and `stream` (default: the current one) as a
+        small object for hot actor loops: `hs.step(a_ptr, r_ptr, d_ptr)` queues one step (raw host
+        pointers as ints: uint8 actions in, int32 rewards / uint8 dones out) and `hs.wait()` returns once
+        that step's outputs are in the caller's buffers — one FFI call each, nothing else.  Make a new
+        one after seed() or after changing time_limit / auto_reset."""
+        st = (stream if stream is not None else torch.cuda.current_stream()).cuda_stream
+        g = self.game
+        key = (st, id(g), self.time_limit, g.seed, self.auto_reset)
+        sp = self._steppers.get(key)
+        if sp is None:
+            sp = self._make_stepper(key, st)
+        return HostStepper(self, sp)
 
     def _make_stepper(self, key, st):
         """Bind the per-env-batch arguments once (slb_stepper_create): the per-step FFI call then

@@ -910,3 +910,34 @@ def test_side_effect_counts_runs_and_fixed_points(sl, h, w, num_samples):
         assert sorted(mine) == sorted(int(k) for k in ok), i
         for s, k in enumerate(ok):
             assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
+
+
+@pytest.mark.gpu
+def test_step_host_direct_and_graph_paths(sl):
+    """Host-buffer steps on a side stream: batches of up to 4096 envs take the copy-free path (actions in
+    the launch parameters, outputs published by the step's last CTA), larger ones the cached-graph path
+    with DMA copies; both must equal the device-buffer step, over many steps (sequence numbers) and with
+    two batch sizes sharing one stream's staging block."""
+    lv = gu.levels("append-spawn")
+    pool = sl.game.LevelPool(lv)
+    rng = np.random.RandomState(11)
+    st = torch.cuda.Stream()
+    for n, T in ((4096, 40), (37, 300), (4100, 6)):
+        ref = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=3, global_counter=None, compute_obs=False,
+                                 auto_reset=True, time_limit=25)
+        host = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=3, global_counter=None, compute_obs=False,
+                                  auto_reset=True, time_limit=25)
+        for e in (ref, host):
+            e.seed(2); e.reset()
+        r = torch.zeros(n, dtype=torch.int32).pin_memory()
+        d = torch.zeros(n, dtype=torch.uint8).pin_memory()
+        for t in range(T):
+            a = rng.randint(9, size=n).astype(np.uint8)
+            _, wr, wd, _ = ref.step(torch.from_numpy(a).cuda())
+            host.step_host(a, r, d, sync=False, stream=st)
+            host.wait(st)
+            assert (r.numpy() == wr.cpu().numpy()).all(), (n, t)
+            assert (d.numpy() == wd.cpu().numpy()).all(), (n, t)
+        torch.cuda.synchronize()
+        assert (host.game.state == ref.game.state).all()
+        assert (host.game.board == ref.game.board).all()
