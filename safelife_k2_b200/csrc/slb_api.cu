@@ -482,9 +482,10 @@ struct StepGraph {
     uint8_t *d, *h;  // the staging blocks the graph copies between (a slot's, see below)
 };
 constexpr int kGraphsPerSlot = 32;
+constexpr size_t kIoHeader = 16;  // in front of both blocks: device ticket counter / host sequence word
 struct HostIo {
     cudaStream_t st;
-    uint8_t *d, *h;
+    uint8_t *d, *h;  // the data parts (allocation + kIoHeader)
     size_t cap;
     StepGraph graphs[kGraphsPerSlot];
     int n_graphs;
@@ -507,8 +508,8 @@ HostIo *find_slot(cudaStream_t st) {
 
 void release_slot(HostIo *s) {
     for (int k = 0; k < s->n_graphs; k++) cudaGraphExecDestroy(s->graphs[k].exec);
-    if (s->d) cudaFree(s->d);
-    if (s->h) cudaFreeHost(s->h);
+    if (s->d) cudaFree(s->d - kIoHeader);
+    if (s->h) cudaFreeHost(s->h - kIoHeader);
     memset(s, 0, sizeof(*s));
 }
 
@@ -534,14 +535,20 @@ int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
         SLB_CUDA(cudaStreamSynchronize(st));
         for (int k = 0; k < s->n_graphs; k++) cudaGraphExecDestroy(s->graphs[k].exec);
         s->n_graphs = 0;  // (graphs owned by steppers notice the new blocks and rebuild)
-        if (s->d) cudaFree(s->d);
-        if (s->h) cudaFreeHost(s->h);
+        if (s->d) cudaFree(s->d - kIoHeader);
+        if (s->h) cudaFreeHost(s->h - kIoHeader);
         s->d = s->h = nullptr; s->cap = 0;
-        SLB_CUDA(cudaMalloc(&s->d, need));
-        SLB_CUDA(cudaMallocHost(&s->h, need));
-        SLB_CUDA(cudaMemsetAsync(s->d, 0, need, st));  // the direct path keeps a ticket counter in the block
+        uint8_t *db = nullptr, *hb = nullptr;
+        SLB_CUDA(cudaMalloc(&db, need + kIoHeader));
+        if (cudaMallocHost(&hb, need + kIoHeader) != cudaSuccess) {
+            cudaFree(db);
+            return fail(SLB_ERR_CUDA, "cudaMallocHost failed for the host-step staging block");
+        }
+        // the direct path keeps a ticket counter (device) and the last published step (host) in the headers
+        SLB_CUDA(cudaMemsetAsync(db, 0, need + kIoHeader, st));
         SLB_CUDA(cudaStreamSynchronize(st));
-        memset(s->h, 0, need);
+        memset(hb, 0, need + kIoHeader);
+        s->d = db + kIoHeader; s->h = hb + kIoHeader;
         s->cap = need;
     }
     *out = s;
@@ -582,7 +589,6 @@ bool host_graphs_enabled() {
 }
 
 inline size_t io_off_act(int n) { return ((size_t)5 * n + 15) & ~(size_t)15; }
-inline size_t io_off_ctr(int n) { return (io_off_act(n) + (size_t)n + 15) & ~(size_t)15; }  // ticket counter / sequence word
 
 bool host_direct_enabled() {
     static const bool on = []() { const char *v = getenv("SLB_HOST_DIRECT"); return !v || v[0] != '0'; }();
@@ -622,9 +628,9 @@ int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env
     if (n == 0) return SLB_OK;
     if (int rc = check_pool(pool)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t off_done = (size_t)4 * n, off_act = io_off_act(n), off_ctr = io_off_ctr(n);
+    const size_t off_done = (size_t)4 * n, off_act = io_off_act(n);
     HostIo *s = nullptr;
-    if (int rc = host_io_slot(st, off_ctr + 16, &s)) return rc;
+    if (int rc = host_io_slot(st, off_act + (size_t)n, &s)) return rc;
     if (s->pend_n)  // an earlier step on this stream was never waited for: deliver its outputs first
         if (int rc = finish_pending(s)) return rc;
     uint8_t *d_io = s->d;
@@ -642,8 +648,8 @@ int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env
         memcpy(acts.a, h_actions, (size_t)n);
         HostTail ht;
         ht.d_reward = (int32_t *)d_io; ht.d_done = d_io + off_done;
-        ht.counter = (unsigned *)(d_io + off_ctr);
-        ht.h_block = s->h; ht.h_seq = (uint32_t *)(s->h + off_ctr);
+        ht.counter = (unsigned *)(s->d - kIoHeader);
+        ht.h_block = s->h; ht.h_seq = (uint32_t *)(s->h - kIoHeader);
         ht.seq = ++s->seq;
         if (ht.seq == 0) ht.seq = ++s->seq;  // 0 is the freshly allocated block's value
         launch_res_env_step_host(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, acts, time_limit,
