@@ -214,14 +214,19 @@ int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
  * should overlap their own streams; at most 8 streams with a step in flight per calling thread).  h_actions is consumed
  * before the call returns; h_reward / h_done are valid only after slb_stream_wait(stream), called from
  * the SAME host thread, returns (a plain cudaStreamSynchronize is not enough: on a non-default stream
- * the three operations run as one cached CUDA graph through a page-locked staging block inside the
- * library and slb_stream_wait hands the results over; the host buffers need not be page-locked). */
+ * the step goes through a page-locked staging block inside the library and slb_stream_wait hands the
+ * results over; the host buffers need not be page-locked).  On a non-default stream, batches of up to 4096
+ * envs on boards of 4..32 rows / columns run as ONE kernel launch without any DMA copy: the actions travel
+ * by value in the launch parameters, and the step's last CTA writes reward / done to the page-locked block
+ * and publishes a sequence number that slb_stream_wait spins on (SLB_HOST_DIRECT=0 turns this off).
+ * Other cases run {H2D copy, step, D2H copy} as one cached CUDA graph (SLB_HOST_GRAPH=0: plain calls). */
 int slb_env_step_host_async(const slb_pool *pool, int n, void *d_board, void *d_goals,
                             slb_env_state *d_state, const uint8_t *h_actions, int time_limit,
                             uint64_t seed, uint64_t env_id0, int32_t *h_reward, uint8_t *h_done,
                             int auto_reset_stride, void *stream);
-/* Low-latency wait for everything queued on `stream` (spins on cudaStreamQuery), then delivers the
- * outputs of the slb_env_step_host_async call in flight on it, if any. */
+/* Low-latency wait for the slb_env_step_host_async call in flight on `stream` (spins on the step's
+ * published sequence number, or on cudaStreamQuery where the step ran as copies), then delivers its
+ * outputs; without such a call it waits for everything queued on the stream. */
 int slb_stream_wait(void *stream);
 
 /* A host stepper binds every argument of slb_env_step_host_async that does not change from step to
