@@ -147,9 +147,23 @@ def run_b200(args):
     from safelife_k2_b200.safelife_env import SafeLifeEnv
     from safelife_k2_b200.safelife_game import LevelPool
 
-    rank, world, local = distributed.init_from_env()
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
+    # NCCL may print its version banner on stdout when the communicator is created (first collective):
+    # keep stdout for the one JSON line by pointing fd 1 at stderr until that has happened
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        rank, world, local = distributed.init_from_env()
+        torch.cuda.set_device(local)
+        dev = torch.device("cuda", local)
+        if world > 1:
+            torch.distributed.barrier(device_ids=[local])
+            distributed.max_over_ranks(0.0, dev)
+            torch.cuda.synchronize()
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     n = args.envs
     lo = rank * n
     lv = append_still_levels()
