@@ -120,15 +120,57 @@ __device__ __forceinline__ ColSums col_sums(const BigNbr &nb) {
 }
 
 // >= 2 of the nine: some column holds two, or two columns hold an odd number
-template <int K>
-__device__ __forceinline__ uint32_t nine_two(const BigNbr &nb) {
+template <int K, class NB>
+__device__ __forceinline__ uint32_t nine_two(const NB &nb) {
     const ColSums c = col_sums<K>(nb);
     return or3(c.cl, c.cm, c.cr) | maj3(c.sl, c.sm, c.sr);
 }
 
-// n == 3 / n == 4 of the nine (the adder tree of physics_planes)
+// The same summaries with the left / right words taken from the neighbouring LANES instead of shared
+// memory: when a row is a power-of-two number of words (<= 32) and the item loop advances by a multiple
+// of 32, the words of a row sit in adjacent lanes of one warp, so every lane reduces only its own
+// column of three words (3 loads instead of 9, a third of the row-reduction arithmetic) and fetches its
+// neighbours' reduced words with two shuffles each (segmented: lane +-1 wraps inside the row's lanes,
+// which is the torus).  All 32 lanes must call.
+struct BigNbrW {
+    const uint32_t *um, *mm, *dm;
+    int ll, lr;  // lanes holding the word to the left / right in the same row
+};
+
+__device__ __forceinline__ BigNbrW big_nbr_w(const uint32_t *src, const BigGeo &g, int r, int j) {
+    const int ru = (r == 0) ? g.h - 1 : r - 1, rd = (r == g.h - 1) ? 0 : r + 1;
+    BigNbrW nb;
+    nb.um = src + (ru * g.wpr + j) * BIG_SRC;
+    nb.mm = src + (r * g.wpr + j) * BIG_SRC;
+    nb.dm = src + (rd * g.wpr + j) * BIG_SRC;
+    const int lane = threadIdx.x & 31, seg = lane & ~(g.wpr - 1);
+    nb.ll = seg | ((lane - 1) & (g.wpr - 1));
+    nb.lr = seg | ((lane + 1) & (g.wpr - 1));
+    return nb;
+}
+
 template <int K>
-__device__ __forceinline__ void nine_count(const BigNbr &nb, uint32_t &is3, uint32_t &is4) {
+__device__ __forceinline__ uint32_t nine_or(const BigNbrW &nb) {
+    const uint32_t m = or3(nb.um[K], nb.mm[K], nb.dm[K]);
+    const uint32_t l = __shfl_sync(0xffffffffu, m, nb.ll), r = __shfl_sync(0xffffffffu, m, nb.lr);
+    return or3(__funnelshift_l(l, m, 1), m, __funnelshift_r(m, r, 1));
+}
+
+template <int K>
+__device__ __forceinline__ ColSums col_sums(const BigNbrW &nb) {
+    const uint32_t u = nb.um[K], m = nb.mm[K], d = nb.dm[K];
+    const uint32_t s_m = xor3(u, m, d), c_m = maj3(u, m, d);
+    const uint32_t s_l = __shfl_sync(0xffffffffu, s_m, nb.ll), s_r = __shfl_sync(0xffffffffu, s_m, nb.lr);
+    const uint32_t c_l = __shfl_sync(0xffffffffu, c_m, nb.ll), c_r = __shfl_sync(0xffffffffu, c_m, nb.lr);
+    ColSums c;
+    c.sl = __funnelshift_l(s_l, s_m, 1); c.sm = s_m; c.sr = __funnelshift_r(s_m, s_r, 1);
+    c.cl = __funnelshift_l(c_l, c_m, 1); c.cm = c_m; c.cr = __funnelshift_r(c_m, c_r, 1);
+    return c;
+}
+
+// n == 3 / n == 4 of the nine (the adder tree of physics_planes)
+template <int K, class NB>
+__device__ __forceinline__ void nine_count(const NB &nb, uint32_t &is3, uint32_t &is4) {
     const ColSums c = col_sums<K>(nb);
     const uint32_t s0 = xor3(c.sl, c.sm, c.sr), c0 = maj3(c.sl, c.sm, c.sr);
     const uint32_t s1 = xor3(c.cl, c.cm, c.cr), c1 = maj3(c.cl, c.cm, c.cr);
@@ -166,6 +208,73 @@ struct BigSmem {
     int *warp_tot;    // [BIG_THREADS / 32]
 };
 
+template <bool WARP> struct BigNbrSel;
+template <> struct BigNbrSel<false> {
+    typedef BigNbr type;
+    static __device__ __forceinline__ BigNbr make(const uint32_t *src, const BigGeo &g, int r, int j) { return big_nbr(src, g, r, j); }
+};
+template <> struct BigNbrSel<true> {
+    typedef BigNbrW type;
+    static __device__ __forceinline__ BigNbrW make(const uint32_t *src, const BigGeo &g, int r, int j) { return big_nbr_w(src, g, r, j); }
+};
+
+// Phase B of big_physics: the rule for every item of the board.  WARP: left / right words come from the
+// neighbouring lanes (BigNbrW); the lazily evaluated summaries are then decided per warp (votes), not
+// per item, because every lane has to take part in the shuffles.
+template <bool WARP>
+__device__ __forceinline__ void big_rule_items(uint32_t *planes, const BigGeo &g, unsigned groups,
+                                               const BigSmem &sm, int any7) {
+    const int T = blockDim.x;
+    for (int it = threadIdx.x; it < g.items; it += T) {
+        int r, j;
+        big_row_word(g, it, r, j);
+        typename BigNbrSel<WARP>::type nb = BigNbrSel<WARP>::make(sm.src, g, r, j);
+        const uint32_t rf = sm.rowf[(r == 0) ? g.h - 1 : r - 1] | sm.rowf[r] | sm.rowf[(r == g.h - 1) ? 0 : r + 1];
+        const bool want_f = WARP ? __any_sync(0xffffffffu, (rf & 1u) != 0u) : (rf & 1u) != 0u;
+        const bool want_s = WARP ? __any_sync(0xffffffffu, (rf & 2u) != 0u) : (rf & 2u) != 0u;
+        uint32_t P[16];
+        const unsigned live = groups & (3u | sm.elig[it]);  // phase A left the item's group flags here
+        big_load(planes, g, it, live, P);
+        const uint32_t a = P[0], fz = P[4];
+        uint32_t is3, is4;
+        nine_count<0>(nb, is3, is4);
+        const uint32_t die0 = a & ~(fz | is3 | is4);
+        const uint32_t open0 = ~(a | fz);
+        uint32_t PR = 0, IH = 0;
+        if (want_f) {
+            PR = nine_or<1>(nb);
+            IH = nine_or<2>(nb);
+        }
+        const uint32_t die = die0 & ~PR;
+        const uint32_t open = open0 & ~IH;
+        const uint32_t birth = open & is3;
+        uint32_t elig = 0;
+        if (want_s) elig = open & ~is3 & nine_or<3>(nb);
+        if (any7) sm.elig[it] = elig;
+        const uint32_t flip = die | birth;
+        uint32_t nD = 0, nR = 0, nG = 0, nB = 0;
+        if (WARP ? __any_sync(0xffffffffu, birth != 0u) : birth != 0u) {
+            nD = birth & nine_two<4>(nb);
+            uint32_t tR = nine_two<5>(nb);
+            uint32_t tG = nine_two<6>(nb);
+            uint32_t tB = nine_two<7>(nb);
+            if (want_s) {
+                tR |= nine_or<8>(nb);
+                tG |= nine_or<9>(nb);
+                tB |= nine_or<10>(nb);
+            }
+            nR = birth & tR; nG = birth & tG; nB = birth & tB;
+        }
+        if (flip) {
+            const uint32_t keep = ~flip;
+#pragma unroll
+            for (int b = 0; b < 16; b++) P[b] &= keep;
+            P[0] |= birth; P[3] |= nD; P[9] |= nR; P[10] |= nG; P[11] |= nB;
+            big_store(planes, g, it, live, P);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // One advance_board step of the CTA's board, in place on its resident planes (advance_board.c:34-120,
 // closed form of SURVEY Appendix A; same lazy-but-exact evaluation as physics_planes, per item).
@@ -195,6 +304,9 @@ __device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsign
         s[8] = sp & P[9];
         s[9] = sp & P[10];
         s[10] = sp & P[11];
+        // which of the two rarely populated plane groups hold anything in this item: phase B neither
+        // loads nor stores a group that is all zero here (no rule can create a bit in it)
+        sm.elig[it] = ((P[1] | P[5] | P[6] | P[8]) ? 4u : 0u) | ((sp | P[12] | P[13] | P[14]) ? 8u : 0u);
         const uint32_t f = ((P[5] | P[6]) ? 1u : 0u) | (sp ? 2u : 0u);
         if (f) {
             int r, j;
@@ -205,51 +317,11 @@ __device__ inline uint64_t big_physics(uint32_t *planes, const BigGeo &g, unsign
     }
     const int any7 = __syncthreads_or(has7);  // also the barrier between the phases
     // ---- phase B: rule per item ----
-    for (int it = threadIdx.x; it < g.items; it += T) {
-        int r, j;
-        big_row_word(g, it, r, j);
-        const BigNbr nb = big_nbr(sm.src, g, r, j);
-        const uint32_t rf = sm.rowf[(r == 0) ? g.h - 1 : r - 1] | sm.rowf[r] | sm.rowf[(r == g.h - 1) ? 0 : r + 1];
-        uint32_t P[16];
-        big_load(planes, g, it, groups, P);
-        const uint32_t a = P[0], fz = P[4];
-        uint32_t is3, is4;
-        nine_count<0>(nb, is3, is4);
-        const uint32_t die0 = a & ~(fz | is3 | is4);
-        const uint32_t open0 = ~(a | fz);
-        uint32_t PR = 0, IH = 0;
-        if (rf & 1u) {
-            PR = nine_or<1>(nb);
-            IH = nine_or<2>(nb);
-        }
-        const uint32_t die = die0 & ~PR;
-        const uint32_t open = open0 & ~IH;
-        const uint32_t birth = open & is3;
-        uint32_t elig = 0;
-        if (rf & 2u) elig = open & ~is3 & nine_or<3>(nb);
-        if (any7) sm.elig[it] = elig;
-        const uint32_t flip = die | birth;
-        if (flip) {
-            uint32_t nD = 0, nR = 0, nG = 0, nB = 0;
-            if (birth) {
-                nD = birth & nine_two<4>(nb);
-                uint32_t tR = nine_two<5>(nb);
-                uint32_t tG = nine_two<6>(nb);
-                uint32_t tB = nine_two<7>(nb);
-                if (rf & 2u) {
-                    tR |= nine_or<8>(nb);
-                    tG |= nine_or<9>(nb);
-                    tB |= nine_or<10>(nb);
-                }
-                nR = birth & tR; nG = birth & tG; nB = birth & tB;
-            }
-            const uint32_t keep = ~flip;
-#pragma unroll
-            for (int b = 0; b < 16; b++) P[b] &= keep;
-            P[0] |= birth; P[3] |= nD; P[9] |= nR; P[10] |= nG; P[11] |= nB;
-            big_store(planes, g, it, groups, P);
-        }
-    }
+    // rows that are a power-of-two number of words, whole warps of items: neighbours through the warp
+    if (g.wshift >= 0 && g.wpr <= 32 && (g.items & 31) == 0 && (T & 31) == 0)
+        big_rule_items<true>(planes, g, groups, sm, any7);
+    else
+        big_rule_items<false>(planes, g, groups, sm, any7);
     if (!any7) return counter;  // uniform
     // ---- spawn draws ----
     // (1) raster-order rank of every eligible cell: CTA-wide scan over the items' popcounts; the ranks
