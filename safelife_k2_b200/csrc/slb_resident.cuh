@@ -26,6 +26,9 @@ namespace slb {
 #ifndef SLB_RES_WARPS
 #define SLB_RES_WARPS 4
 #endif
+#ifndef SLB_RES_SLOTS
+#define SLB_RES_SLOTS 28  // resident warps per SM the step kernels are compiled for (register budget)
+#endif
 constexpr int RES_WARPS = SLB_RES_WARPS;  // warps (= envs) per CTA
 
 inline bool fast_shape(int h, int w) { return h >= 4 && w >= 4 && h <= 32 && w <= 32; }
@@ -192,7 +195,7 @@ __device__ __forceinline__ int env_step_once(const slb_pool &pool, const Geo &g,
 // HW: board height = width when known at compile time (26: the benchmark levels), 0 = run time.
 // ONE: exactly one step per launch (the policy-in-the-loop case): no step loop, no action look-ahead.
 template <unsigned GB, unsigned GG, int HW, bool ONE>
-__global__ void __launch_bounds__(RES_WARPS * 32, 28 / RES_WARPS)
+__global__ void __launch_bounds__(RES_WARPS * 32, SLB_RES_SLOTS / RES_WARPS)
 res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                        const uint8_t *__restrict__ actions, int t_steps, int time_limit,
                        uint64_t seed, uint64_t env_id0, int32_t *reward_out, uint8_t *done_out,
@@ -316,7 +319,7 @@ struct HostTail {
 };
 
 template <unsigned GB, unsigned GG, int HW>
-__global__ void __launch_bounds__(RES_WARPS * 32, 28 / RES_WARPS)
+__global__ void __launch_bounds__(RES_WARPS * 32, SLB_RES_SLOTS / RES_WARPS)
 res_env_step_host_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                          const __grid_constant__ ActBlock acts, int time_limit, uint64_t seed,
                          uint64_t env_id0, int auto_reset_stride, HostTail ht) {
@@ -784,7 +787,7 @@ struct ObsArgs {
 };
 
 template <unsigned GB, unsigned GG, int HW, bool CHANNELS, bool IDENT>
-__global__ void __launch_bounds__(RES_WARPS * 32, 28 / RES_WARPS)
+__global__ void __launch_bounds__(RES_WARPS * 32, SLB_RES_SLOTS / RES_WARPS)
 res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                         const uint8_t *__restrict__ actions, int time_limit, uint64_t seed, uint64_t env_id0,
                         int32_t *reward_out, uint8_t *done_out, int auto_reset_stride, int l2_prefetch,
