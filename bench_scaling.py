@@ -33,9 +33,23 @@ def main():
     ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=3)
     args = ap.parse_args()
-    rank, world, local = distributed.init_from_env()
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
+    # keep stdout for the one JSON line: NCCL prints its version banner there when the communicator is made
+    import os
+    import sys
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        rank, world, local = distributed.init_from_env()
+        torch.cuda.set_device(local)
+        dev = torch.device("cuda", local)
+        if world > 1:
+            torch.distributed.barrier(device_ids=[local])
+            torch.cuda.synchronize()
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
     if args.workload == "mixed_26":
         parts = [gu.levels(a) for a in gu.ARCHIVES]
         lv = {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
