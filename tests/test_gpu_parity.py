@@ -941,3 +941,45 @@ def test_step_host_direct_and_graph_paths(sl):
         torch.cuda.synchronize()
         assert (host.game.state == ref.game.state).all()
         assert (host.game.board == ref.game.board).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("h,w", [(9, 31), (32, 32), (5, 7)])
+def test_step_host_direct_path_vs_oracle(sl, h, w):
+    """The copy-free host-buffer step (res_env_step_host_kernel, every plane-group / runtime-shape
+    variant: dense random levels carry spawners on boards AND goals) against the oracle, step by step,
+    with auto-reset, through the bound hot-loop stepper (SafeLifeEnv.host_stepper)."""
+    rng = np.random.RandomState(h * 31 + w)
+    lv = _random_levels(rng, 24, h, w)
+    n, steps = 130, 50  # not a multiple of the 4 envs per CTA: the last CTA has idle warps
+    pool = sl.game.LevelPool(lv)
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=9, global_counter=None, auto_reset=True, time_limit=20,
+                             compute_obs=False)
+    env.seed(h)
+    env.reset()
+    lvl = (np.arange(n) + 9) % pool.n_levels
+    oenv = slo.OracleBatchEnv(slo.OraclePool(**lv), lvl, seed=h, env_id0=9, threads=4, time_limit=20)
+    stride = n % pool.n_levels or pool.n_levels
+    st = torch.cuda.Stream()
+    hs = env.host_stepper(st)
+    a = torch.zeros(n, dtype=torch.uint8).pin_memory()
+    r = torch.zeros(n, dtype=torch.int32).pin_memory()
+    d = torch.zeros(n, dtype=torch.uint8).pin_memory()
+    for t in range(steps):
+        acts = rng.randint(9, size=n)
+        a.copy_(torch.from_numpy(acts.astype(np.uint8)))
+        hs.step(a.data_ptr(), r.data_ptr(), d.data_ptr())
+        hs.wait()
+        orr, od = oenv.step(acts)
+        assert (r.numpy() == orr).all(), t
+        assert (d.numpy() == (od != 0)).all(), t
+        if od.any():
+            idx = np.nonzero(od)[0]
+            lvl[idx] = (lvl[idx] + stride) % pool.n_levels
+            oenv.reset(idx, lvl[idx])
+    torch.cuda.synchronize()
+    assert (env.game.board.cpu().numpy() == oenv.boards).all()
+    assert (env.game.goals.cpu().numpy() == oenv.goals).all()
+    stt, ost = env.game.state_numpy(), oenv.states
+    for f in stt.dtype.names:
+        assert (stt[f] == ost[f]).all(), f
