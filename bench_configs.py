@@ -9,6 +9,7 @@ judged line for config 2).  Prints one JSON line per configuration:
   big_256             config 5b: 4096 envs at 256x256 (synthetic levels of SURVEY §8(d)), k=1
   side_effects        config 4: side_effect_score counts (1000 samples) for finished prune-spawn episodes
   obs                 get_obs 15x15x15 for 4096 envs
+  env_step_api        wall clock of SafeLifeEnv.step (device actions in, observation out) per call
   int_peak            LOP3 / LOP3+IMAD issue-rate microbenchmark (denominator of the integer roofline)
 
     python bench_configs.py [names...] [--quick]
@@ -96,7 +97,7 @@ def synth_256(rng5, rng6, p):
 
 def main():
     names = [a for a in sys.argv[1:] if not a.startswith("--")] or ["prune_spawn_16384", "mixed_65536", "rollout_k32",
-                                                                   "big_256", "side_effects", "step_obs", "obs", "int_peak"]
+                                                                   "big_256", "side_effects", "step_obs", "obs", "env_step_api", "int_peak"]
     quick = "--quick" in sys.argv
     out = []
     if "prune_spawn_16384" in names:
@@ -250,6 +251,27 @@ def main():
         ms = timed(env.get_obs, 200)
         out.append({"config": "obs", "envs": n, "view": [15, 15, 15], "ms_per_call": ms, "obs_per_s": n / ms * 1e3,
                     "write_GBps": n * 15 * 15 * 15 * 2 / (ms * 1e-3) / 1e9})
+    if "env_step_api" in names:
+        # the gym-style call a GPU policy makes: env.step(device actions) -> (obs, reward, done, info), wall clock
+        pool = LevelPool(gu.levels("append-still"))
+        n = 4096
+        env = SafeLifeEnv(pool, num_envs=n, global_counter=None, auto_reset=True)
+        env.seed(0)
+        env.reset()
+        acts = torch.from_numpy(np.random.RandomState(3).randint(9, size=(n,)).astype(np.uint8)).cuda()
+        for _ in range(200):
+            env.step(acts)
+        torch.cuda.synchronize()
+        reps = 300 if quick else 3000
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            obs, r, d, info = env.step(acts)
+        host = time.perf_counter() - t0
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        out.append({"config": "env_step_api", "envs": n, "view": [15, 15, 15], "us_per_call_host": host / reps * 1e6,
+                    "us_per_call": dt / reps * 1e6, "env_steps_per_s": n * reps / dt,
+                    "what": "SafeLifeEnv.step with uint8 cuda actions, fused step + observation, python call path included"})
     if "int_peak" in names:
         # the integer roofline's denominator, measured here: LOP3 chains on every scheduler
         import ctypes

@@ -42,25 +42,51 @@ class HostStepper(object):
 
 
 class _Info(dict):
-    """The step's info dict (safelife_env.py:176-186).  'board' and 'goals' are uint16 [N,H,W]
-    tensors exported from the resident state when first asked for, not on every step."""
+    """The step's info dict (safelife_env.py:176-186): 'board', 'goals' (uint16 [N,H,W] tensors exported
+    from the resident state), 'agent_loc', 'times_up', 'episode'.  Every value is read from the env state
+    when it is first asked for, not on every step: a policy loop that never looks at them pays nothing
+    for them.  Read them before the next step() — the state they come from moves on."""
+    _KEYS = ("board", "goals", "agent_loc", "times_up", "episode")
 
-    def __init__(self, game, items):
-        super().__init__(items)
-        self._game = game
+    def __init__(self, game, time_limit):
+        super().__init__()
+        self._game, self._time_limit = game, time_limit
 
     def __missing__(self, key):
+        g = self._game
         if key in ("board", "goals"):
-            val = getattr(self._game, key)
-            self[key] = val
-            return val
-        raise KeyError(key)
+            val = getattr(g, key)
+        elif key == "agent_loc":
+            val = g.agent_loc
+        elif key == "times_up":
+            val = g._field("episode_length") > self._time_limit
+        elif key == "episode":
+            val = {"length": g._field("episode_length"), "reward": g._field("episode_reward")}
+        else:
+            raise KeyError(key)
+        self[key] = val
+        return val
+
+    def get(self, key, default=None):
+        return self[key] if key in self._KEYS else super().get(key, default)
 
     def keys(self):
-        return list(super().keys() | {"board", "goals"})
+        return list(super().keys() | set(self._KEYS))
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def __len__(self):
+        return len(self.keys())
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+    def values(self):
+        return [self[k] for k in self.keys()]
 
     def __contains__(self, key):
-        return key in ("board", "goals") or super().__contains__(key)
+        return key in self._KEYS or super().__contains__(key)
 
 
 class SafeLifeEnv(object):
@@ -177,45 +203,51 @@ class SafeLifeEnv(object):
         return self._ch
 
     def step(self, action):
-        """action: int array/tensor [N] (0..8).  Returns (obs, reward int32 [N], done bool [N], info)."""
-        assert self.game is not None, "Game state is not initialized."
+        """action: int array/tensor [N] (0..8).  Returns (obs, reward int32 [N], done bool [N], info).
+        The call path is kept short for a policy on the GPU: a contiguous uint8 cuda tensor of actions is
+        used as it is, `done` is a bool view of the step's uint8 output, `info` is filled on access."""
         g = self.game
-        acts = g._actions(action)
+        assert g is not None, "Game state is not initialized."
+        if (type(action) is torch.Tensor and action.dtype == torch.uint8 and action.is_cuda
+                and action.numel() == g.n and action.is_contiguous()):
+            acts = action
+        else:
+            acts = g._actions(action)
         already = g._field("episode_completed").clone() if self.global_counter is not None else None
         obs = None
-        with torch.cuda.device(self.pool.device):
-            stride = self._stride() if self.auto_reset else 0
-            if self.compute_obs and self._fused_obs:
-                # step and observation in one launch (slb_env_step_obs) where the shapes allow it
-                vh, vw = self.view_shape
-                ch = self._channels() if self.output_channels else None
-                shape = (g.n, vh, vw, ch.size) if ch is not None else (g.n, vh, vw)
-                obs = torch.empty(shape, dtype=torch.uint16, device=self.pool.device)
-                rc = self._lib.slb_env_step_obs(
-                    self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                    acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
-                    self._done.data_ptr(), stride, vh, vw, int(self.remove_white_goals),
-                    ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0,
-                    obs.data_ptr(), _lib.current_stream())
-                if rc == _lib.SLB_ERR_UNSUPPORTED:
-                    self._fused_obs, obs = False, None
-                else:
-                    _lib.check(rc)
-            if obs is None:
-                _lib.check(self._lib.slb_env_step(
-                    self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                    acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
-                    self._done.data_ptr(), stride, _lib.current_stream()))
-        done = self._done != 0
+        if torch.cuda.current_device() != self._dev_index:
+            torch.cuda.set_device(self._dev_index)
+        st = torch.cuda.current_stream().cuda_stream
+        stride = self._stride() if self.auto_reset else 0
+        if self.compute_obs and self._fused_obs:
+            # step and observation in one launch (slb_env_step_obs) where the shapes allow it
+            vh, vw = self.view_shape
+            ch = self._channels() if self.output_channels else None
+            shape = (g.n, vh, vw, ch.size) if ch is not None else (g.n, vh, vw)
+            obs = torch.empty(shape, dtype=torch.uint16, device=self.pool.device)
+            rc = self._lib.slb_env_step_obs(
+                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+                acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
+                self._done.data_ptr(), stride, vh, vw, int(self.remove_white_goals),
+                ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0,
+                obs.data_ptr(), st)
+            if rc == _lib.SLB_ERR_UNSUPPORTED:
+                self._fused_obs, obs = False, None
+            elif rc:
+                _lib.check(rc)
+        if obs is None:
+            rc = self._lib.slb_env_step(
+                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+                acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
+                self._done.data_ptr(), stride, st)
+            if rc:
+                _lib.check(rc)
+        done = self._done.view(torch.bool).clone()  # the step writes 0 / 1; a fresh tensor every step
         if self.global_counter is not None:
             fresh = already == 0
             self.global_counter.episodes_completed += int((done & fresh).sum().item())
             self.global_counter.num_steps += int(fresh.sum().item())
-        info = _Info(g, {
-            "agent_loc": g.agent_loc,
-            "times_up": g._field("episode_length") > self.time_limit,
-            "episode": {"length": g._field("episode_length"), "reward": g._field("episode_reward")},
-        })
+        info = _Info(g, self.time_limit)
         if obs is None and self.compute_obs:
             obs = self.get_obs()
         return obs, self._reward, done, info
