@@ -11,7 +11,8 @@ Differences from the reference, by design:
   * a non-2-D / empty board raises ValueError (the reference returns NULL without an exception set,
     i.e. SystemError, module.c:29-32);
   * ``gen_pattern`` and ``wrapped_label`` are procedural-generation natives that stay in the
-    reference extension (north_star); they are not provided here.
+    reference extension (north_star): they delegate to ``safelife.speedups`` when the reference package
+    is importable and raise NotImplementedError otherwise.
 """
 import numpy as np
 
@@ -88,12 +89,39 @@ def _advance_tensor(board, spawn_prob):
     return out
 
 
+def _reference_ext():
+    """The reference's own extension module, if the reference package is installed next to this one."""
+    try:
+        from safelife import speedups as ref  # noqa: PLC0415  (the reference package, not part of this repo)
+        return ref
+    except Exception:
+        return None
+
+
 def gen_pattern(*args, **kwargs):
-    raise NotImplementedError(
-        "gen_pattern is procedural generation: it stays in the reference C extension "
-        "(safelife.speedups.gen_pattern) and feeds the level pool from the host")
+    """Procedural generation stays in the reference C extension (north_star; module.c:129-243): this
+    delegates to ``safelife.speedups.gen_pattern`` when the reference package is importable."""
+    ref = _reference_ext()
+    if ref is None:
+        raise NotImplementedError(
+            "gen_pattern is procedural generation: it stays in the reference C extension "
+            "(safelife.speedups.gen_pattern) and feeds the level pool from the host")
+    return ref.gen_pattern(*args, **kwargs)
 
 
 def wrapped_label(*args, **kwargs):
-    raise NotImplementedError(
-        "wrapped_label is a procgen/analysis helper that stays in the reference C extension")
+    """module.c:65-88; delegates to the reference extension like gen_pattern."""
+    ref = _reference_ext()
+    if ref is None:
+        raise NotImplementedError(
+            "wrapped_label is a procgen/analysis helper that stays in the reference C extension")
+    return ref.wrapped_label(*args, **kwargs)
+
+
+def __getattr__(name):
+    # BoardGenException and its subclasses (module.c:298-309) live in the reference extension
+    if name in ("BoardGenException", "MaxIterException", "BadProbabilityException", "InsufficientAreaException"):
+        ref = _reference_ext()
+        if ref is not None:
+            return getattr(ref, name)
+    raise AttributeError("module %r has no attribute %r" % (__name__, name))

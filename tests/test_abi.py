@@ -64,3 +64,30 @@ def test_product_does_not_touch_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.replace("parity oracle", ""), f
                 assert "slo_" not in text, f
+
+
+def test_procgen_natives_delegate_to_the_reference_extension(monkeypatch):
+    """speedups.gen_pattern / wrapped_label / the BoardGen exceptions stay in the reference extension
+    (SURVEY 8(b)): delegated when `safelife.speedups` is importable, NotImplementedError otherwise."""
+    import sys
+    import types
+
+    import pytest
+
+    from safelife_k2_b200 import speedups
+
+    monkeypatch.setitem(sys.modules, "safelife", None)  # not importable
+    with pytest.raises(NotImplementedError):
+        speedups.gen_pattern(None, None, 1)
+    with pytest.raises(AttributeError):
+        speedups.BoardGenException
+    pkg, ext = types.ModuleType("safelife"), types.ModuleType("safelife.speedups")
+    ext.gen_pattern = lambda *a, **k: ("gen", a, k)
+    ext.wrapped_label = lambda data: ("label", data)
+    ext.BoardGenException = type("BoardGenException", (Exception,), {})
+    pkg.speedups = ext
+    monkeypatch.setitem(sys.modules, "safelife", pkg)
+    monkeypatch.setitem(sys.modules, "safelife.speedups", ext)
+    assert speedups.gen_pattern(1, 2, period=3) == ("gen", (1, 2), {"period": 3})
+    assert speedups.wrapped_label(7) == ("label", 7)
+    assert speedups.BoardGenException is ext.BoardGenException
