@@ -129,6 +129,42 @@ class LevelPool(object):
         with torch.cuda.device(self.device):
             _lib.check(_lib.load().slb_pool_prepare(self.c, _lib.current_stream()))
 
+    def update(self, slots, levels):
+        """Replace the levels in `slots` (indices into the pool) with new ones of the same board shape —
+        the feed from a host-side level generator (the reference's procedural generation, proc_gen.py via
+        speedups.gen_pattern, stays on the host): envs pick the new levels up at their next reset /
+        auto-reset into those slots.  An env that is IN an episode on one of the slots keeps its board but
+        would see the new level's constants (baseline, exit cells, min_performance): update slots that no
+        env is playing, or reset those envs right after.  Re-prepares the pool (slb_pool_prepare)."""
+        rec = _stack_levels(levels)
+        slots = np.asarray(slots, dtype=np.int64).reshape(-1)
+        if rec["board"].shape != (slots.size, self.h, self.w):
+            raise ValueError("need one %dx%d level per slot" % (self.h, self.w))
+        if slots.size and (slots.min() < 0 or slots.max() >= self.n_levels):
+            raise ValueError("slot out of range")
+        idx = torch.from_numpy(slots).to(self.device)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)  # noqa: E731
+        if not getattr(self, "_host_owned", False):  # never write through to the caller's arrays
+            self.host = {k: np.array(v) for k, v in self.host.items()}
+            self._host_owned = True
+        for k in rec:
+            self.host[k][slots] = rec[k]
+        self.board.view(torch.int16)[idx] = t(rec["board"]).view(torch.int16)
+        self.goals.view(torch.int16)[idx] = t(rec["goals"]).view(torch.int16)
+        self.agent_x[idx] = t(rec["agent_loc"][:, 0].astype(np.int32))
+        self.agent_y[idx] = t(rec["agent_loc"][:, 1].astype(np.int32))
+        self.orientation[idx] = t(rec["orientation"].astype(np.int32))
+        self.spawn_prob[idx] = t(rec["spawn_prob"].astype(np.float32))
+        self.min_performance[idx] = t(rec["min_performance"].astype(np.float64))
+        if self.names is not None:
+            new_names = _level_names(levels)
+            for j, sl in enumerate(slots):
+                self.names[sl] = new_names[j] if new_names else "level-%d" % sl
+        keep = int(self.c.external_writes)  # out-of-band board writes stay known across the re-prepare
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().slb_pool_prepare(self.c, _lib.current_stream()))
+        self.c.external_writes = keep
+
 
 def _stack_levels(levels):
     keys = ("board", "goals", "agent_loc", "orientation", "spawn_prob", "min_performance")

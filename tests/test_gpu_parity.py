@@ -983,3 +983,46 @@ def test_step_host_direct_path_vs_oracle(sl, h, w):
     stt, ost = env.game.state_numpy(), oenv.states
     for f in stt.dtype.names:
         assert (stt[f] == ost[f]).all(), f
+
+
+@pytest.mark.gpu
+def test_level_pool_update_feeds_new_levels(sl):
+    """LevelPool.update: slots refilled from the host (the procedural-generation feed) are what envs play
+    after their next reset, bit-exact with an oracle pool that held those levels from the start; envs on
+    untouched slots are not disturbed."""
+    base = gu.level_slice(gu.levels("prune-spawn"), 0, 8)
+    fresh = gu.level_slice(gu.levels("append-spawn"), 10, 12)
+    pool = sl.game.LevelPool(base)
+    n = 16
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False, auto_reset=True, time_limit=30)
+    env.seed(4)
+    env.reset()
+    rng = np.random.RandomState(1)
+    for _ in range(10):
+        env.step(rng.randint(9, size=n))
+    pool.update([2, 5], fresh)
+    merged = {k: np.array(base[k]) for k in base}
+    for k in merged:
+        merged[k][[2, 5]] = fresh[k]
+    assert (pool.board.cpu().numpy() == merged["board"]).all() and (pool.goals.cpu().numpy() == merged["goals"]).all()
+    # a second env batch on the same pool starts from the merged level set
+    env2 = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False, auto_reset=True, time_limit=30)
+    env2.seed(6)
+    env2.reset()
+    lvl = np.arange(n) % 8
+    oenv = slo.OracleBatchEnv(slo.OraclePool(**merged), lvl, seed=6, env_id0=0, threads=2, time_limit=30)
+    stride = n % 8 or 8
+    for t in range(80):
+        acts = rng.randint(9, size=n)
+        _, r, d, _ = env2.step(acts)
+        orr, od = oenv.step(acts)
+        assert (r.cpu().numpy() == orr).all() and (d.cpu().numpy() == (od != 0)).all(), t
+        if od.any():
+            idx = np.nonzero(od)[0]
+            lvl[idx] = (lvl[idx] + stride) % 8
+            oenv.reset(idx, lvl[idx])
+    assert (env2.game.board.cpu().numpy() == oenv.boards).all()
+    assert (env2.game.goals.cpu().numpy() == oenv.goals).all()
+    stt, ost = env2.game.state_numpy(), oenv.states
+    for f in stt.dtype.names:
+        assert (stt[f] == ost[f]).all(), f
