@@ -545,8 +545,10 @@ int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
             return fail(SLB_ERR_CUDA, "cudaMallocHost failed for the host-step staging block");
         }
         // the direct path keeps a ticket counter (device) and the last published step (host) in the headers
-        SLB_CUDA(cudaMemsetAsync(db, 0, need + kIoHeader, st));
-        SLB_CUDA(cudaStreamSynchronize(st));
+        if (cudaMemset(db, 0, need + kIoHeader) != cudaSuccess) {  // synchronous, not tied to `st`
+            cudaFree(db); cudaFreeHost(hb);
+            return fail(SLB_ERR_CUDA, "cudaMemset failed for the host-step staging block");
+        }
         memset(hb, 0, need + kIoHeader);
         s->d = db + kIoHeader; s->h = hb + kIoHeader;
         s->cap = need;
