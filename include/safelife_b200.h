@@ -291,6 +291,19 @@ int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, 
                      int remove_white_goals, const uint8_t *h_channels, int n_channels, uint16_t *d_obs,
                      void *stream);
 
+/* SafeLifeEnv.step for a policy on the GPU (safelife_env.py:157-186) with everything that does not change
+ * from step to step bound once: step = slb_env_step_obs (vh > 0 and d_obs given; SLB_ERR_UNSUPPORTED where
+ * that call is) or slb_env_step, rewards going to the d_reward given at creation.  h_channels is copied.
+ * `pool` must outlive the stepper. */
+typedef struct slb_dev_stepper slb_dev_stepper;
+int slb_dev_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                           int time_limit, uint64_t seed, uint64_t env_id0, int auto_reset_stride,
+                           int32_t *d_reward, int vh, int vw, int remove_white_goals,
+                           const uint8_t *h_channels, int n_channels, slb_dev_stepper **out);
+int slb_dev_stepper_step(slb_dev_stepper *s, const uint8_t *d_actions, uint8_t *d_done, uint16_t *d_obs,
+                         void *stream);
+void slb_dev_stepper_destroy(slb_dev_stepper *s);
+
 /* The channel split of safelife_env.py:152-154 for M packed words: d_out [M, n_channels] uint16,
  * d_out[m, c] = (d_words[m] >> h_channels[c]) & 1.  h_channels: n_channels <= 16 bit indices in HOST
  * memory (read before the call returns); d_out 16-byte aligned. */

@@ -72,6 +72,10 @@ SYMBOLS = {
     "slb_get_obs_channels": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "slb_side_effect_penalty": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp]),
     "slb_obs_channels": (_i, [_vp, _sz, _vp, _i, _vp, _vp]),
+    "slb_dev_stepper_create": (_i, [_PP, _i, _vp, _vp, _vp, _i, _u64, _u64, _i, _vp, _i, _i, _i, _vp, _i,
+                                    C.POINTER(_vp)]),
+    "slb_dev_stepper_step": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "slb_dev_stepper_destroy": (None, [_vp]),
     "slb_microbench_int": (_i, [_i, _i, _i, _vp, C.POINTER(_u64), _vp]),
 }
 

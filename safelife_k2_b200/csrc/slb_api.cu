@@ -960,6 +960,46 @@ int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, 
     return SLB_OK;
 }
 
+// ---- device-buffer step with every per-batch argument bound once (the GPU-policy loop) -----------
+struct slb_dev_stepper {
+    const slb_pool *pool;
+    int n, time_limit, stride;
+    void *board, *goals;
+    slb_env_state *state;
+    uint64_t seed, env_id0;
+    int32_t *reward;
+    int vh, vw, remove_white, n_channels;  // vh == 0: no observation
+    uint8_t channels[16];
+};
+
+int slb_dev_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                           int time_limit, uint64_t seed, uint64_t env_id0, int auto_reset_stride,
+                           int32_t *d_reward, int vh, int vw, int remove_white_goals,
+                           const uint8_t *h_channels, int n_channels, slb_dev_stepper **out) {
+    if (int rc = check_pool(pool)) return rc;
+    if (!out || n < 0 || !d_board || !d_goals || !d_state || vh < 0 || vw < 0 || n_channels < 0 || n_channels > 16 ||
+        (n_channels > 0 && !h_channels))
+        return fail(SLB_ERR_INVALID, "slb_dev_stepper_create: bad arguments");
+    slb_dev_stepper *s = new slb_dev_stepper{pool, n, time_limit, auto_reset_stride, d_board, d_goals, d_state,
+                                             seed, env_id0, d_reward, vh, vw, remove_white_goals, n_channels, {}};
+    for (int c = 0; c < n_channels; c++) s->channels[c] = h_channels[c];
+    *out = s;
+    return SLB_OK;
+}
+
+int slb_dev_stepper_step(slb_dev_stepper *s, const uint8_t *d_actions, uint8_t *d_done, uint16_t *d_obs,
+                         void *stream) {
+    if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
+    if (s->vh > 0 && d_obs)
+        return slb_env_step_obs(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
+                                s->env_id0, s->reward, d_done, s->stride, s->vh, s->vw, s->remove_white,
+                                s->n_channels ? s->channels : nullptr, s->n_channels, d_obs, stream);
+    return slb_env_step(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
+                        s->env_id0, s->reward, d_done, s->stride, stream);
+}
+
+void slb_dev_stepper_destroy(slb_dev_stepper *s) { delete s; }
+
 int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *h_channels, int n_channels,
                      uint16_t *d_out, void *stream) {
     if (!d_words || !d_out) return fail(SLB_ERR_INVALID, "slb_obs_channels: bad arguments");

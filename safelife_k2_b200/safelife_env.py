@@ -120,6 +120,7 @@ class SafeLifeEnv(object):
         self._seed = 0
         self._lib = _lib.load()
         self._steppers = {}
+        self._dev_sp, self._dev_key, self._obs_shape = None, None, None
         self._obs_scratch = False
         self._fused_obs = True
         self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
@@ -214,35 +215,28 @@ class SafeLifeEnv(object):
         else:
             acts = g._actions(action)
         already = g._field("episode_completed").clone() if self.global_counter is not None else None
-        obs = None
         if torch.cuda.current_device() != self._dev_index:
             torch.cuda.set_device(self._dev_index)
         st = torch.cuda.current_stream().cuda_stream
-        stride = self._stride() if self.auto_reset else 0
-        if self.compute_obs and self._fused_obs:
-            # step and observation in one launch (slb_env_step_obs) where the shapes allow it
-            vh, vw = self.view_shape
-            ch = self._channels() if self.output_channels else None
-            shape = (g.n, vh, vw, ch.size) if ch is not None else (g.n, vh, vw)
-            obs = torch.empty(shape, dtype=torch.uint16, device=self.pool.device)
-            rc = self._lib.slb_env_step_obs(
-                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
-                self._done.data_ptr(), stride, vh, vw, int(self.remove_white_goals),
-                ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0,
-                obs.data_ptr(), st)
-            if rc == _lib.SLB_ERR_UNSUPPORTED:
-                self._fused_obs, obs = False, None
-            elif rc:
-                _lib.check(rc)
-        if obs is None:
-            rc = self._lib.slb_env_step(
-                self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
-                acts.data_ptr(), int(self.time_limit), g.seed, g.env_id0, self._reward.data_ptr(),
-                self._done.data_ptr(), stride, st)
-            if rc:
-                _lib.check(rc)
-        done = self._done.view(torch.bool).clone()  # the step writes 0 / 1; a fresh tensor every step
+        # every argument that does not change from step to step is bound once in a native stepper
+        oc = self.output_channels
+        key = (id(g), self.time_limit, g.seed, self.auto_reset, self.view_shape, tuple(oc) if oc else None,
+               self.remove_white_goals, self.compute_obs, self._fused_obs)
+        if key != self._dev_key:
+            self._bind_dev_stepper(key)
+        dev = self.pool.device
+        done = torch.empty(g.n, dtype=torch.bool, device=dev)  # the step writes 0 / 1; fresh every step
+        self._done = done.view(torch.uint8)
+        obs = torch.empty(self._obs_shape, dtype=torch.uint16, device=dev) if self._obs_shape is not None else None
+        rc = self._dev_step(self._dev_sp, acts.data_ptr(), done.data_ptr(), obs.data_ptr() if obs is not None else None, st)
+        if rc == _lib.SLB_ERR_UNSUPPORTED and obs is not None:
+            # this board / view shape has no fused step + observation: step, then get_obs
+            self._fused_obs = False
+            self._bind_dev_stepper(key[:-1] + (False,))
+            obs = None
+            rc = self._dev_step(self._dev_sp, acts.data_ptr(), done.data_ptr(), None, st)
+        if rc:
+            _lib.check(rc)
         if self.global_counter is not None:
             fresh = already == 0
             self.global_counter.episodes_completed += int((done & fresh).sum().item())
@@ -251,6 +245,26 @@ class SafeLifeEnv(object):
         if obs is None and self.compute_obs:
             obs = self.get_obs()
         return obs, self._reward, done, info
+
+    def _bind_dev_stepper(self, key):
+        import ctypes
+        g = self.game
+        if self._dev_sp is not None:
+            self._lib.slb_dev_stepper_destroy(self._dev_sp)
+            self._dev_sp = None
+        fused = self.compute_obs and self._fused_obs
+        vh, vw = self.view_shape if fused else (0, 0)
+        ch = self._channels() if (fused and self.output_channels) else None
+        self._obs_shape = None
+        if fused:
+            self._obs_shape = (g.n, vh, vw, ch.size) if ch is not None else (g.n, vh, vw)
+        out = ctypes.c_void_p()
+        _lib.check(self._lib.slb_dev_stepper_create(
+            self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
+            int(self.time_limit), g.seed, g.env_id0, self._stride() if self.auto_reset else 0,
+            self._reward.data_ptr(), vh, vw, int(self.remove_white_goals),
+            ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0, ctypes.byref(out)))
+        self._dev_sp, self._dev_key, self._dev_step = out, key, self._lib.slb_dev_stepper_step
 
     def step_host(self, actions_host, reward_host, done_host, sync=True, stream=None):
         """Host-buffer step (slb_env_step_host): uint8 actions in host memory in, int32 rewards / uint8
@@ -305,6 +319,9 @@ class SafeLifeEnv(object):
         for sp in self._steppers.values():
             self._lib.slb_stepper_destroy(sp)
         self._steppers.clear()
+        if self._dev_sp is not None:
+            self._lib.slb_dev_stepper_destroy(self._dev_sp)
+            self._dev_sp, self._dev_key = None, None
 
     def __del__(self):
         try:
