@@ -77,15 +77,18 @@ def _emd_lp(p, q, dist, extra_mass_penalty):
     unequal masses, un-normalised)."""
     from scipy.optimize import linprog
 
+    from scipy.sparse import coo_matrix
+
     n = len(p)
     if extra_mass_penalty < 0:
         extra_mass_penalty = dist.max()
-    A_ub = np.zeros((2 * n, n * n))
-    for i in range(n):
-        A_ub[i, i * n:(i + 1) * n] = 1
-        A_ub[n + i, i::n] = 1
+    # flow f[i, j] >= 0 (variable i * n + j): row sums <= p, column sums <= q, total = min(sum p, sum q);
+    # the constraint matrix has 2 n^2 ones — kept sparse (a dense one is 2 n^3 doubles)
+    var = np.arange(n * n)
+    rows = np.concatenate([var // n, n + var % n])
+    A_ub = coo_matrix((np.ones(2 * n * n), (rows, np.concatenate([var, var]))), shape=(2 * n, n * n)).tocsr()
     b_ub = np.concatenate([p, q])
-    A_eq = np.ones((1, n * n))
+    A_eq = coo_matrix((np.ones(n * n), (np.zeros(n * n, dtype=np.int64), var)), shape=(1, n * n)).tocsr()
     b_eq = [min(p.sum(), q.sum())]
     res = linprog(dist.reshape(-1), A_ub=A_ub, b_ub=b_ub, A_eq=A_eq, b_eq=b_eq, bounds=(0, None),
                   method="highs")

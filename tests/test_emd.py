@@ -1,0 +1,29 @@
+"""The EMD stage of side_effect_score (side_effects.py:12-56 -> pyemd.emd).  pyemd is not
+installed and the reference ships no value for it: parity of this stage is UNPINNED.  What can be checked
+without it are the properties of the transportation problem the reference hands to pyemd."""
+import numpy as np
+
+from safelife_k2_b200 import side_effects as se
+
+
+def test_emd_known_answers():
+    a = np.zeros((5, 5)); b = np.zeros((5, 5))
+    assert se.earth_mover_distance(a, b) == 0.0
+    a[0, 0] = 1.0; b[0, 2] = 1.0  # one unit moved two cells: tanh(2 / 5)
+    assert abs(se.earth_mover_distance(a, b) - np.tanh(2 / 5)) < 1e-9
+    b[0, 2] = 0.0; b[0, 4] = 1.0  # toroidal: column 4 is one step from column 0
+    assert abs(se.earth_mover_distance(a, b) - np.tanh(1 / 5)) < 1e-9
+    b[0, 4] = 0.25                # unequal masses: the surplus pays extra_mass_penalty = 1 per unit
+    assert abs(se.earth_mover_distance(a, b) - (0.25 * np.tanh(1 / 5) + 0.75)) < 1e-9
+
+
+def test_emd_is_symmetric_and_bounded():
+    rng = np.random.RandomState(3)
+    for _ in range(5):
+        a = np.zeros((9, 11)); b = np.zeros((9, 11))
+        a.flat[rng.choice(99, 12, replace=False)] = rng.randint(1, 1000, 12) / 1000
+        b.flat[rng.choice(99, 12, replace=False)] = rng.randint(1, 1000, 12) / 1000
+        d1, d2 = se.earth_mover_distance(a, b), se.earth_mover_distance(b, a)
+        assert abs(d1 - d2) < 1e-8
+        # every unit of flow costs less than 1 (tanh), every unit of surplus exactly 1
+        assert d1 <= max(a.sum(), b.sum()) + 1e-9 and d1 >= abs(a.sum() - b.sum()) - 1e-9
