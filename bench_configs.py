@@ -9,6 +9,7 @@ judged line for config 2).  Prints one JSON line per configuration:
   big_256             config 5b: 4096 envs at 256x256 (synthetic levels of SURVEY §8(d)), k=1
   side_effects        config 4: side_effect_score counts (1000 samples) for finished prune-spawn episodes
   obs                 get_obs 15x15x15 for 4096 envs
+  advance_board       the speedups.advance_board contract: uint16 boards in / out, k = 1 and k = 32
   env_step_api        wall clock of SafeLifeEnv.step (device actions in, observation out) per call
   int_peak            LOP3 / LOP3+IMAD issue-rate microbenchmark (denominator of the integer roofline)
 
@@ -97,7 +98,7 @@ def synth_256(rng5, rng6, p):
 
 def main():
     names = [a for a in sys.argv[1:] if not a.startswith("--")] or ["prune_spawn_16384", "mixed_65536", "rollout_k32",
-                                                                   "big_256", "side_effects", "step_obs", "obs", "env_step_api", "int_peak"]
+                                                                   "big_256", "side_effects", "step_obs", "obs", "advance_board", "env_step_api", "int_peak"]
     quick = "--quick" in sys.argv
     out = []
     if "prune_spawn_16384" in names:
@@ -251,6 +252,28 @@ def main():
         ms = timed(env.get_obs, 200)
         out.append({"config": "obs", "envs": n, "view": [15, 15, 15], "ms_per_call": ms, "obs_per_s": n / ms * 1e3,
                     "write_GBps": n * 15 * 15 * 15 * 2 / (ms * 1e-3) / 1e9})
+    if "advance_board" in names:
+        # A1, the speedups.advance_board contract itself: N uint16 boards in, N new uint16 boards out
+        # (4 B per cell-update at k = 1), boards larger than L2 in total; k = 32 steps fused on chip beside it
+        n = 8192 if quick else 131072
+        lib, st = _lib.load(), torch.cuda.current_stream().cuda_stream
+        p = torch.full((n,), 0.3, dtype=torch.float32, device="cuda")
+        for arch in ("append-still", "prune-spawn"):
+            lv = gu.levels(arch)
+            idx = torch.arange(n, device="cuda") % lv["board"].shape[0]
+            src = torch.from_numpy(lv["board"]).cuda().view(torch.int16)[idx].contiguous().view(torch.uint16)
+            dst = torch.empty_like(src)
+            for k in (1, 32):
+                def go():
+                    _lib.check(lib.slb_advance_board(src.data_ptr(), dst.data_ptr(), n, 26, 26, p.data_ptr(), 0, 0, None,
+                                                     k, None, st))
+                ms = timed(go, 5 if quick else 20, warm=3)
+                cu = n * 676 * k
+                out.append({"config": "advance_board_%s_k%d" % (arch, k), "boards": n, "board": [26, 26], "k_steps": k,
+                            "ms_per_call": ms, "cell_updates_per_s": cu / ms * 1e3,
+                            "hbm_frac": (n * 676 * 4 / (ms * 1e-3) / 1e9 / HBM) if k == 1 else None,
+                            "what": "slb_advance_board (the speedups.advance_board contract: uint16 boards in, new uint16 "
+                                    "boards out), one stream per board"})
     if "env_step_api" in names:
         # the gym-style call a GPU policy makes: env.step(device actions) -> (obs, reward, done, info), wall clock
         pool = LevelPool(gu.levels("append-still"))
