@@ -18,30 +18,57 @@ __host__ __device__ inline bool fast_vec_ok(int h, int w, const void *a, const v
 // ---------------------------------------------------------------------------------------------
 // A1: advance_board, k steps on chip.  grid = ceil(N / FAST_WARPS).
 // ---------------------------------------------------------------------------------------------
+template <int HW>  // HW = 26: the benchmark board size at compile time; 0: runtime shape
 __global__ void __launch_bounds__(FAST_WARPS * 32)
-advance_fast_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int n, int h, int w,
+advance_fast_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int n, int h_, int w_,
                     const float *__restrict__ spawn_prob, uint64_t seed, uint64_t env_id0,
                     uint64_t *counters, int k_steps, bool vec) {
     __shared__ __align__(16) uint16_t stage[FAST_WARPS][FAST_STAGE_U16];
     const int warp = threadIdx.x >> 5, i = blockIdx.x * FAST_WARPS + warp;
     if (i >= n) return;
+    const int h = HW ? HW : h_, w = HW ? HW : w_;
     const Geo g = make_geo(h, w);
     const size_t cells = (size_t)h * w;
     uint32_t P[16];
-    load_planes(in + i * cells, stage[warp], h, w, vec, P);
+    load_planes<HW>(in + i * cells, stage[warp], h, w, vec, P);
     uint64_t counter = counters ? counters[i] : 0;
     const float p = spawn_prob[i];
-    bool ch;
-    for (int k = 0; k < k_steps; k++) counter = physics_planes(P, g, p, seed, env_id0 + i, counter, ch);
-    store_planes(out + i * cells, stage[warp], h, w, vec, P);
+    bool ch, any_ch = false;
+    for (int k = 0; k < k_steps; k++) {
+        counter = physics_planes(P, g, p, seed, env_id0 + i, counter, ch);
+        any_ch |= ch;
+    }
+    if (any_ch) {
+        store_planes<HW>(out + i * cells, stage[warp], h, w, vec, P);
+    } else {
+        // nothing changed (warp-uniform): the staging area still holds the input image — copy it out
+        // instead of transposing the planes back
+        const int lane = threadIdx.x & 31, S = row_stride(w);
+        uint16_t *dst = out + i * cells;
+        const uint16_t *sm = stage[warp];
+        if (vec) {
+            const uint2 *s2 = reinterpret_cast<const uint2 *>(sm);
+            uint2 *d2 = reinterpret_cast<uint2 *>(dst);
+            for (int j = lane; j < ((int)cells >> 2); j += 32) d2[j] = s2[j];
+        } else {
+            for (int e = lane; e < (int)cells; e += 32) {
+                int r = e / w, c = e - r * w;
+                dst[e] = sm[r * S + c];
+            }
+        }
+    }
     if (counters && (threadIdx.x & 31) == 0) counters[i] = counter;
 }
 
 inline void launch_advance_fast(const uint16_t *in, uint16_t *out, int n, int h, int w, const float *p,
                                 uint64_t seed, uint64_t env0, uint64_t *ctr, int k, cudaStream_t st) {
     int grid = (n + FAST_WARPS - 1) / FAST_WARPS;
-    advance_fast_kernel<<<grid, FAST_WARPS * 32, 0, st>>>(in, out, n, h, w, p, seed, env0, ctr, k,
-                                                          fast_vec_ok(h, w, in, out));
+    if (h == 26 && w == 26)
+        advance_fast_kernel<26><<<grid, FAST_WARPS * 32, 0, st>>>(in, out, n, h, w, p, seed, env0, ctr, k,
+                                                                  fast_vec_ok(h, w, in, out));
+    else
+        advance_fast_kernel<0><<<grid, FAST_WARPS * 32, 0, st>>>(in, out, n, h, w, p, seed, env0, ctr, k,
+                                                                 fast_vec_ok(h, w, in, out));
 }
 
 }  // namespace slb

@@ -102,8 +102,11 @@ __host__ __device__ __forceinline__ int row_stride(int w) {
 }
 
 // vec: all boards are 8-byte aligned and S == w (then the smem image equals the memory image)
-__device__ __forceinline__ void load_planes(const uint16_t *__restrict__ src, uint16_t *sm, int h,
-                                            int w, bool vec, uint32_t P[16]) {
+// HW > 0: the board is HW x HW, known at compile time (row predicates and strides fold away).
+template <int HW = 0>
+__device__ __forceinline__ void load_planes(const uint16_t *__restrict__ src, uint16_t *sm, int h_,
+                                            int w_, bool vec, uint32_t P[16]) {
+    const int h = HW ? HW : h_, w = HW ? HW : w_;
     const int lane = threadIdx.x & 31, cells = h * w, S = row_stride(w);
     __syncwarp();
     if (vec) {
@@ -131,8 +134,10 @@ __device__ __forceinline__ void load_planes(const uint16_t *__restrict__ src, ui
     cells_to_planes(x, P);
 }
 
-__device__ __forceinline__ void store_planes(uint16_t *__restrict__ dst, uint16_t *sm, int h, int w,
+template <int HW = 0>
+__device__ __forceinline__ void store_planes(uint16_t *__restrict__ dst, uint16_t *sm, int h_, int w_,
                                              bool vec, const uint32_t P[16]) {
+    const int h = HW ? HW : h_, w = HW ? HW : w_;
     const int lane = threadIdx.x & 31, cells = h * w, S = row_stride(w);
     uint32_t x[16];
     planes_to_cells(P, x);
