@@ -54,6 +54,16 @@ def test_argument_checks_without_gpu():
     assert L.slb_pool_prepare(None, None) == _lib.SLB_ERR_INVALID
     assert L.slb_side_effect_counts(a, a, 1, 4, 4, a, 10, a, 0, 0, None, 1000, a, a, a, None, None) \
         == _lib.SLB_ERR_INVALID
+    # the bound steppers and the measurement aid reject bad arguments before touching the device
+    out = ctypes.c_void_p()
+    assert L.slb_stepper_create(None, 1, a, a, a, 1000, 0, 0, 0, None, ctypes.byref(out)) == _lib.SLB_ERR_INVALID
+    assert L.slb_stepper_step(None, a, a, a) == _lib.SLB_ERR_INVALID
+    assert L.slb_stepper_wait(None) == _lib.SLB_ERR_INVALID
+    assert L.slb_dev_stepper_create(None, 1, a, a, a, 1000, 0, 0, 0, a, 15, 15, 1, None, 0, ctypes.byref(out)) \
+        == _lib.SLB_ERR_INVALID
+    assert L.slb_dev_stepper_step(None, a, a, a, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_microbench_int(2, 1, 1, a, None, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_microbench_int(0, 0, 1, a, None, None) == _lib.SLB_ERR_INVALID
 
 
 def test_product_does_not_touch_the_oracle():
