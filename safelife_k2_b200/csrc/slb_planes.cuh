@@ -16,6 +16,7 @@ struct Geo {
     int h, w;
     int up, dn;      // source lanes of the rows above / below this lane (toroidal)
     uint32_t wmask;  // low W bits
+    uint32_t hib;    // 1 << (W - 1): multiplying by it moves column 0 to column W - 1
     bool row;        // lane < h
 };
 
@@ -27,6 +28,7 @@ __device__ __forceinline__ Geo make_geo(int h, int w) {
     g.up = g.row ? (lane == 0 ? h - 1 : lane - 1) : lane;
     g.dn = g.row ? (lane == h - 1 ? 0 : lane + 1) : lane;
     g.wmask = (w >= 32) ? 0xffffffffu : ((1u << w) - 1u);
+    g.hib = 1u << (w - 1);
     return g;
 }
 
@@ -36,6 +38,17 @@ __device__ __forceinline__ uint32_t from_left(uint32_t x, const Geo &g) {
 }
 __device__ __forceinline__ uint32_t from_right(uint32_t x, const Geo &g) {
     return ((x >> 1) | (x << (g.w - 1))) & g.wmask;
+}
+
+// The same neighbours WITHOUT the final mask: columns 0 .. W-1 are right, bits >= W hold rubbish.  For
+// values that are only combined column by column and ANDed with a clean plane before they are stored or
+// rotated again (every summary of the step below): a shift plus a multiply-add instead of two shifts and
+// a masked OR, and the multiply-add issues on the FMA pipe, which the bit-sliced code leaves idle.
+__device__ __forceinline__ uint32_t from_left_raw(uint32_t x, const Geo &g) {
+    return x * 2u + (x >> (g.w - 1));          // bit 0 of 2x is clear: the sum is an OR
+}
+__device__ __forceinline__ uint32_t from_right_raw(uint32_t x, const Geo &g) {
+    return x * g.hib + (x >> 1);               // x * hib: column 0 -> column W-1, the rest above it
 }
 
 __device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) { return a ^ b ^ c; }
@@ -170,9 +183,10 @@ __device__ __forceinline__ void store_planes(uint16_t *__restrict__ dst, uint16_
 // per board).  A board on which nothing dies, nothing can be born and no spawner exists costs the
 // count and three votes.
 // ---------------------------------------------------------------------------------------------
+// (box_or / box_two: columns 0 .. W-1 only — bits >= W of the result are rubbish, see from_left_raw)
 __device__ __forceinline__ uint32_t box_or(uint32_t x, const Geo &g) {  // OR over the 3x3, centre included
     const uint32_t v = or3(x, __shfl_sync(FULL, x, g.up), __shfl_sync(FULL, x, g.dn));
-    return or3(from_left(v, g), v, from_right(v, g));
+    return or3(from_left_raw(v, g), v, from_right_raw(v, g));
 }
 
 // ">= 2 of the alive cells in the 3x3 carry the flag" (pairwise AND accumulation of
@@ -180,8 +194,8 @@ __device__ __forceinline__ uint32_t box_or(uint32_t x, const Geo &g) {  // OR ov
 __device__ __forceinline__ uint32_t box_two(uint32_t src, const Geo &g) {
     const uint32_t u = __shfl_sync(FULL, src, g.up), d = __shfl_sync(FULL, src, g.dn);
     const uint32_t f0 = xor3(src, u, d), f1 = maj3(src, u, d);  // column count, 2 bits
-    const uint32_t hi = or3(from_left(f1, g), f1, from_right(f1, g));
-    return hi | maj3(from_left(f0, g), f0, from_right(f0, g));
+    const uint32_t hi = or3(from_left_raw(f1, g), f1, from_right_raw(f1, g));
+    return hi | maj3(from_left_raw(f0, g), f0, from_right_raw(f0, g));
 }
 
 // The step is split into "compute what flips" and "apply it" so that a caller can still use the old
@@ -204,8 +218,8 @@ __device__ __forceinline__ uint64_t physics_compute(const uint32_t P[16], const 
     {
         const uint32_t u = __shfl_sync(FULL, a, g.up), d = __shfl_sync(FULL, a, g.dn);
         const uint32_t v0 = xor3(a, u, d), v1 = maj3(a, u, d);
-        const uint32_t l0 = from_left(v0, g), r0 = from_right(v0, g);
-        const uint32_t l1 = from_left(v1, g), r1 = from_right(v1, g);
+        const uint32_t l0 = from_left_raw(v0, g), r0 = from_right_raw(v0, g);
+        const uint32_t l1 = from_left_raw(v1, g), r1 = from_right_raw(v1, g);
         const uint32_t s0 = xor3(l0, v0, r0), c0 = maj3(l0, v0, r0);
         const uint32_t s1 = xor3(l1, v1, r1), c1 = maj3(l1, v1, r1);
         const uint32_t n1 = c0 ^ s1, k = c0 & s1, n2 = c1 ^ k;
