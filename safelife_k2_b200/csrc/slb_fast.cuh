@@ -33,19 +33,44 @@ advance_fast_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out,
     load_planes<HW>(in + i * cells, stage[warp], h, w, vec, P);
     uint64_t counter = counters ? counters[i] : 0;
     const float p = spawn_prob[i];
-    bool ch, any_ch = false;
-    for (int k = 0; k < k_steps; k++) {
-        counter = physics_planes(P, g, p, seed, env_id0 + i, counter, ch);
-        any_ch |= ch;
+    uint32_t touched = 0;  // this lane's cells that flipped (single step), or all ones once anything changed
+    if (k_steps == 1) {
+        PhysDelta dl;
+        bool quiet;
+        counter = physics_compute(P, g, p, seed, env_id0 + i, counter, dl, quiet);
+        if (__any_sync(FULL, dl.flip != 0)) {
+            physics_apply(P, dl);
+            touched = dl.flip;
+        }
+    } else {
+        bool ch, any_ch = false;
+        for (int k = 0; k < k_steps; k++) {
+            counter = physics_planes(P, g, p, seed, env_id0 + i, counter, ch);
+            any_ch |= ch;
+        }
+        if (any_ch) touched = 0xffffffffu;  // several steps: take the full back-transposition
     }
-    if (any_ch) {
+    const int lane = threadIdx.x & 31;
+    const int most = __reduce_max_sync(FULL, __popc(touched));  // busiest row
+    if (most > 8) {
         store_planes<HW>(out + i * cells, stage[warp], h, w, vec, P);
     } else {
-        // nothing changed (warp-uniform): the staging area still holds the input image — copy it out
-        // instead of transposing the planes back
-        const int lane = threadIdx.x & 31, S = row_stride(w);
+        // Few cells changed (or none): the staging area still holds the input image.  A cell that flipped
+        // lost every bit and, where it was born, got alive / destructible / colour bits only (physics_apply),
+        // so its final value is read off five planes and patched into the image, which is then copied out —
+        // no back-transposition of the planes.
+        const int S = row_stride(w);
+        uint16_t *sm = stage[warp];
+        uint32_t t = touched;
+        while (t) {
+            const int x = __ffs(t) - 1;
+            t &= t - 1;
+            const uint32_t v = ((P[0] >> x) & 1u) | (((P[3] >> x) & 1u) << 3) | (((P[9] >> x) & 1u) << 9) |
+                               (((P[10] >> x) & 1u) << 10) | (((P[11] >> x) & 1u) << 11);
+            sm[lane * S + x] = (uint16_t)v;
+        }
+        __syncwarp();
         uint16_t *dst = out + i * cells;
-        const uint16_t *sm = stage[warp];
         if (vec) {
             const uint2 *s2 = reinterpret_cast<const uint2 *>(sm);
             uint2 *d2 = reinterpret_cast<uint2 *>(dst);
