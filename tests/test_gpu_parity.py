@@ -1026,3 +1026,38 @@ def test_level_pool_update_feeds_new_levels(sl):
     stt, ost = env2.game.state_numpy(), oenv.states
     for f in stt.dtype.names:
         assert (stt[f] == ost[f]).all(), f
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("h,w", [(26, 26), (13, 20), (32, 32)])
+def test_advance_board_batch_sparse_and_dense(sl, h, w):
+    """slb_advance_board on a batch that mixes the kernel's write-back paths: boards on which nothing
+    changes (copied out), boards with a few flipped cells per row (patched into the staged image) and
+    dense soups (full back-transposition), with spawners and all 16 cell bits, k = 1 and k = 3, each
+    board on its own stream, against the oracle."""
+    rng = np.random.RandomState(h * 7 + w)
+    n = 48
+    boards = np.zeros((n, h, w), np.uint16)
+    for i in range(n):
+        kind = i % 4
+        if kind == 0:    # still life + walls: nothing changes
+            boards[i, 2:4, 2:4] = 1033
+            boards[i, 0, :] = 16
+        elif kind == 1:  # a few blinkers / a glider: a handful of flips
+            boards[i, 5, 3:6] = 521
+            boards[i, h - 3, w - 4:w - 1] = 1033
+            boards[i, 1, 1] = 1688
+        elif kind == 2:  # dense soup of typical cell types
+            vals = np.array([0, 0, 0, 1033, 521, 16, 17, 1688, 32788, 2057], np.uint16)
+            boards[i] = vals[rng.randint(len(vals), size=(h, w))]
+        else:            # noise over all 16 bits, sparse
+            boards[i] = np.where(rng.rand(h, w) < 0.15, rng.randint(0, 65536, size=(h, w)), 0).astype(np.uint16)
+    ctr0 = rng.randint(0, 500, size=n).astype(np.int64)
+    for k in (1, 3):
+        out, ctr = dev_advance(sl, boards, 0.3, 21, 1000, ctr0, k=k)
+        for i in range(n):
+            b, c = boards[i], int(ctr0[i])
+            for _ in range(k):
+                b, c = slo.advance_board(b, 0.3, seed=21, env=1000 + i, counter=c)
+            assert (out[i] == b).all(), (k, i)
+            assert ctr[i] == c, (k, i)
