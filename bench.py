@@ -275,7 +275,7 @@ def run_b200(args):
     # loop: while one batch's results travel back, the next batches step); each step's outputs are waited
     # for before that batch's buffers are reused.
     e2e_steps = min(K, 5000)
-    depth = 4
+    depth = int(os.environ.get("SLB_BENCH_DEPTH", "6"))
     h_act = torch.from_numpy(rng.randint(9, size=(n_act, n)).astype(np.uint8)).pin_memory()
     h_out = [torch.zeros(5 * n, dtype=torch.uint8).pin_memory() for _ in range(depth)]
     streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]

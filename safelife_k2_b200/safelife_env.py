@@ -11,6 +11,8 @@ output_channels, global_counter (safelife_env.py:73-95).
 """
 from types import SimpleNamespace
 
+import os
+
 import numpy as np
 import torch
 
@@ -27,8 +29,14 @@ class HostStepper(object):
     __slots__ = ("_env", "_sp", "_step", "_wait", "_dev")
 
     def __init__(self, env, sp):
-        self._env, self._sp, self._dev = env, sp, env._dev_index
-        self._step, self._wait = env._lib.slb_stepper_step, env._lib.slb_stepper_wait
+        self._env, self._dev = env, env._dev_index
+        try:  # the CPython binding of the two calls (csrc/slb_pyfast.c): no ctypes marshalling per step
+            if os.environ.get("SLB_NO_PYFAST"):
+                raise ImportError
+            from . import _slbfast
+            self._sp, self._step, self._wait = sp.value, _slbfast.step, _slbfast.wait
+        except ImportError:  # not built: the same two C-ABI calls through ctypes
+            self._sp, self._step, self._wait = sp, env._lib.slb_stepper_step, env._lib.slb_stepper_wait
 
     def step(self, actions_ptr, reward_ptr, done_ptr):
         rc = self._step(self._sp, actions_ptr, reward_ptr, done_ptr)
