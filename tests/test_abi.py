@@ -101,3 +101,15 @@ def test_procgen_natives_delegate_to_the_reference_extension(monkeypatch):
     assert speedups.gen_pattern(1, 2, period=3) == ("gen", (1, 2), {"period": 3})
     assert speedups.wrapped_label(7) == ("label", 7)
     assert speedups.BoardGenException is ext.BoardGenException
+
+
+def test_fast_binding_of_the_host_step_calls():
+    """safelife_k2_b200/_slbfast (csrc/slb_pyfast.c, built by build()): the CPython binding of
+    slb_stepper_step / slb_stepper_wait lands in the same library instance as the ctypes handle."""
+    from safelife_k2_b200 import _lib, _slbfast
+
+    L = _lib.load()
+    assert _slbfast.step(0, 0, 0, 0) == _lib.SLB_ERR_INVALID
+    assert b"stepper is NULL" in L.slb_last_error()
+    assert _slbfast.wait(0) == _lib.SLB_ERR_INVALID
+    assert _slbfast.step(None, None, None, None) == _lib.SLB_ERR_INVALID
