@@ -495,7 +495,7 @@ __device__ inline void big_score(const uint32_t *board, const uint32_t *goals, c
                                  const uint32_t *e0, bool skip_exits, int *scratch, int &pts, int &cur,
                                  int &pos) {
     Geo full;
-    full.h = g.h; full.w = 32; full.up = full.dn = 0; full.wmask = 0xffffffffu; full.row = true;
+    full.h = g.h; full.w = 32; full.up = full.dn = 0; full.wmask = 0xffffffffu; full.hib = 0x80000000u; full.row = true;
     pts = cur = pos = 0;
     for (int it = threadIdx.x; it < g.items; it += blockDim.x) {
         uint32_t B[16], G[16];
