@@ -363,7 +363,17 @@ res_env_step_host_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals,
         const int nvec = (5 * n + 15) >> 4;
         const uint4 *src = reinterpret_cast<const uint4 *>(ht.d_reward);
         uint4 *dst = reinterpret_cast<uint4 *>(ht.h_block);
-        for (int j = threadIdx.x; j < nvec; j += blockDim.x) dst[j] = __ldcg(src + j);
+        // (four loads in flight per thread: the copy is this CTA's alone and every load is an L2 round trip)
+        const int T = blockDim.x;
+        for (int j = threadIdx.x; j < nvec; j += 4 * T) {
+            uint4 v[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (j + q * T < nvec) v[q] = __ldcg(src + j + q * T);
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (j + q * T < nvec) dst[j + q * T] = v[q];
+        }
         __threadfence_system();
         __syncthreads();
         if (threadIdx.x == 0) {
