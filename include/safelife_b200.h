@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SLB_ABI_VERSION 3
+#define SLB_ABI_VERSION 4
 
 typedef enum {
     SLB_OK = 0,
@@ -48,7 +48,7 @@ int slb_abi_version(void);
 uint64_t slb_launch_count(void);
 
 /* Per-env scalar state (replaces the GameState/SafeLifeEnv attributes listed in SURVEY.md A6/A12:
- * safelife_game.py:155-168, safelife_env.py:162-175,190-195).  64 bytes, one per env. */
+ * safelife_game.py:155-168, safelife_env.py:162-175,190-195).  80 bytes, one per env, 16-byte aligned. */
 typedef struct {
     int32_t agent_x, agent_y;     /* GameState.agent_loc (x, y) */
     int32_t orientation;          /* 0 up, 1 right, 2 down, 3 left */
@@ -62,7 +62,14 @@ typedef struct {
     int32_t completed, possible;  /* last performance_ratio() */
     int64_t episode_reward;       /* SafeLifeEnv.episode_reward */
     uint64_t rng_counter;         /* next draw index of this env's stream */
+    double min_performance;       /* GameState.min_performance (safelife_game.py:166): the level's value at
+                                     reset; a wrapper may overwrite it (slb_env_set_min_performance) */
+    uint32_t flags;               /* SLB_ENV_RESCORE */
+    uint32_t reserved;
 } slb_env_state;
+/* the next step re-evaluates score, can_exit and the exit colours even if nothing on the board changed
+ * (set when something the cached values depend on was changed from outside; cleared by that step) */
+#define SLB_ENV_RESCORE 1u
 
 /* Level pool on the device (replaces _init_data of each game + the per-level scalars,
  * safelife_game.py:184-212; file_finder.py:78-98 record layout). */
@@ -159,6 +166,14 @@ int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, 
  * For every env i with d_mask == NULL or d_mask[i] != 0: load level d_level_ids[i]. */
 int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const uint8_t *d_mask,
                   void *d_board, void *d_goals, slb_env_state *d_state, void *stream);
+
+/* `game.min_performance = value` for the envs with d_mask == NULL or d_mask[i] != 0 (what the reference's
+ * SimpleSideEffectPenalty.reset does after env.reset(), env_wrappers.py:313-317): stores the value, re-evaluates
+ * can_exit() (safelife_game.py:522-526) from the env's last performance_ratio() so that the next
+ * execute_action sees it, and marks the env so that its next step repaints the exits (the reference's
+ * update_exit_colors runs every step).  The board is not touched: exit colours change at the next step. */
+int slb_env_set_min_performance(int n, slb_env_state *d_state, const uint8_t *d_mask, double value,
+                                void *stream);
 
 /* ---- A7/A8: execute_action (safelife_game.py:347-393, move_agent :308-345) -----------------------
  * d_actions: [N] uint8, 0 NULL, 1-4 MOVE U/R/D/L, 5-8 TOGGLE U/R/D/L (safelife_env.py:61-71).
@@ -293,15 +308,20 @@ int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, 
 
 /* SafeLifeEnv.step for a policy on the GPU (safelife_env.py:157-186) with everything that does not change
  * from step to step bound once: step = slb_env_step_obs (vh > 0 and d_obs given; SLB_ERR_UNSUPPORTED where
- * that call is) or slb_env_step, rewards going to the d_reward given at creation.  h_channels is copied.
- * `pool` must outlive the stepper. */
+ * that call is) or slb_env_step.  Rewards go to the d_reward given to the step, or to the one given at
+ * creation when that is NULL.  h_channels is copied.  `pool` must outlive the stepper.
+ * d_global_counter (may be NULL): SafeLifeEnv.global_counter kept on the device (safelife_env.py:169-173) —
+ * 64 pairs of uint64 {num_steps, episodes_completed}, zeroed by the caller; every step adds, for each env that
+ * was not already done, 1 to num_steps and its `done` to episodes_completed, env i into pair i % 64 (the
+ * caller sums the pairs when it reads the counter; no host synchronisation per step). */
 typedef struct slb_dev_stepper slb_dev_stepper;
 int slb_dev_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
                            int time_limit, uint64_t seed, uint64_t env_id0, int auto_reset_stride,
                            int32_t *d_reward, int vh, int vw, int remove_white_goals,
-                           const uint8_t *h_channels, int n_channels, slb_dev_stepper **out);
-int slb_dev_stepper_step(slb_dev_stepper *s, const uint8_t *d_actions, uint8_t *d_done, uint16_t *d_obs,
-                         void *stream);
+                           const uint8_t *h_channels, int n_channels, uint64_t *d_global_counter,
+                           slb_dev_stepper **out);
+int slb_dev_stepper_step(slb_dev_stepper *s, const uint8_t *d_actions, int32_t *d_reward, uint8_t *d_done,
+                         uint16_t *d_obs, void *stream);
 void slb_dev_stepper_destroy(slb_dev_stepper *s);
 
 /* The channel split of safelife_env.py:152-154 for M packed words: d_out [M, n_channels] uint16,

@@ -33,9 +33,10 @@ ENV_STATE_DTYPE = np.dtype(
         ("episode_completed", "<i4"),
         ("old_points", "<i4"), ("can_exit", "<i4"), ("completed", "<i4"), ("possible", "<i4"),
         ("episode_reward", "<i8"), ("rng_counter", "<u8"),
+        ("min_performance", "<f8"), ("flags", "<u4"), ("reserved", "<u4"),
     ]
 )
-assert ENV_STATE_DTYPE.itemsize == 64
+assert ENV_STATE_DTYPE.itemsize == 80
 
 
 class Pool(C.Structure):

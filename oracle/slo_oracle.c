@@ -304,7 +304,8 @@ static void advance_inplace(uint16_t *cells, uint16_t *tmp, int h, int w, float 
     memcpy(cells, tmp, (size_t)h * w * sizeof(uint16_t));
 }
 
-static int eval_can_exit_cp(const slo_pool *pool, int level, const uint16_t *board,
+/* can_exit() (safelife_game.py:522-526) with the game's own min_performance attribute */
+static int eval_can_exit_cp(const slo_pool *pool, int level, double min_performance, const uint16_t *board,
                             const uint16_t *goals, int32_t *c_out, int32_t *p_out) {
     size_t off = (size_t)level * pool->h * pool->w;
     int64_t base = slo_baseline_score(pool->board + off, pool->goals + off, pool->h, pool->w);
@@ -312,12 +313,12 @@ static int eval_can_exit_cp(const slo_pool *pool, int level, const uint16_t *boa
     slo_performance_ratio(board, goals, pool->h, pool->w, base, &completed, &possible);
     if (c_out) *c_out = (int32_t)completed;
     if (p_out) *p_out = (int32_t)possible;
-    return slo_can_exit(pool->min_performance[level], completed, possible);
+    return slo_can_exit(min_performance, completed, possible);
 }
 
-static int eval_can_exit(const slo_pool *pool, int level, const uint16_t *board,
+static int eval_can_exit(const slo_pool *pool, int level, double min_performance, const uint16_t *board,
                          const uint16_t *goals) {
-    return eval_can_exit_cp(pool, level, board, goals, NULL, NULL);
+    return eval_can_exit_cp(pool, level, min_performance, board, goals, NULL, NULL);
 }
 
 void slo_env_reset(const slo_pool *pool, int level_id, uint16_t *board, uint16_t *goals,
@@ -332,7 +333,10 @@ void slo_env_reset(const slo_pool *pool, int level_id, uint16_t *board, uint16_t
     s->game_over = 0;
     s->num_steps = 0;
     s->level_id = level_id;
-    s->can_exit = eval_can_exit_cp(pool, level_id, board, goals, &s->completed, &s->possible);
+    s->min_performance = pool->min_performance[level_id]; /* deserialize, safelife_game.py:205 */
+    s->flags = 0;
+    s->reserved = 0;
+    s->can_exit = eval_can_exit_cp(pool, level_id, s->min_performance, board, goals, &s->completed, &s->possible);
     slo_update_exit_colors(board, pool->board + off, h, w, s->can_exit);
     s->old_points = (int32_t)slo_current_points(board, goals, h, w);
     s->episode_length = 0;
@@ -357,7 +361,7 @@ int64_t slo_env_step(const slo_pool *pool, uint16_t *board, uint16_t *goals, slo
         int fx, fy;
         forward_vec((action - 1) & 3, &fx, &fy);
         unsigned front = board[(size_t)pymod(s->agent_y + fy, h) * w + pymod(s->agent_x + fx, w)];
-        if (front & C_EXIT) ce = eval_can_exit(pool, level, board, goals);
+        if (front & C_EXIT) ce = eval_can_exit(pool, level, s->min_performance, board, goals);
     }
     int64_t reward = slo_execute_action(board, h, w, s, action, ce);
     /* SafeLifeGame.advance_board :657-660 — board first, then goals (RNG order) */
@@ -370,7 +374,7 @@ int64_t slo_env_step(const slo_pool *pool, uint16_t *board, uint16_t *goals, slo
     s->old_points = (int32_t)pts;
     s->episode_length += 1;
     s->episode_reward += reward;
-    s->can_exit = eval_can_exit_cp(pool, level, board, goals, &s->completed, &s->possible);
+    s->can_exit = eval_can_exit_cp(pool, level, s->min_performance, board, goals, &s->completed, &s->possible);
     slo_update_exit_colors(board, pool->board + off, h, w, s->can_exit);
     int times_up = s->episode_length > time_limit;
     s->episode_completed = times_up || s->game_over;

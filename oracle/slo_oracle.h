@@ -47,7 +47,9 @@ typedef struct {
     int32_t old_points, can_exit, completed, possible;
     int64_t episode_reward;
     uint64_t rng_counter;
-} slo_env_state; /* 64 bytes */
+    double min_performance; /* GameState.min_performance: the level's value after a reset, writable */
+    uint32_t flags, reserved; /* the product's bookkeeping; always 0 here */
+} slo_env_state; /* 80 bytes */
 
 /* safelife_game.py:347-393 for the nine env actions of safelife_env.py:61-71 (0 NULL, 1-4 MOVE
  * U/R/D/L, 5-8 TOGGLE U/R/D/L); move_agent :308-345.  `can_exit` is the value can_exit() would

@@ -52,6 +52,7 @@ SYMBOLS = {
     "slb_advance_board_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _u64, _u64, _vp, _i]),
     "slb_env_reset": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "slb_execute_action": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp]),
+    "slb_env_set_min_performance": (_i, [_i, _vp, _vp, C.c_double, _vp]),
     "slb_game_advance": (_i, [_PP, _i, _vp, _vp, _vp, _u64, _u64, _vp]),
     "slb_points_and_performance": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "slb_update_exit_colors": (_i, [_PP, _i, _vp, _vp, _vp, _vp]),
@@ -73,8 +74,8 @@ SYMBOLS = {
     "slb_side_effect_penalty": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _vp]),
     "slb_obs_channels": (_i, [_vp, _sz, _vp, _i, _vp, _vp]),
     "slb_dev_stepper_create": (_i, [_PP, _i, _vp, _vp, _vp, _i, _u64, _u64, _i, _vp, _i, _i, _i, _vp, _i,
-                                    C.POINTER(_vp)]),
-    "slb_dev_stepper_step": (_i, [_vp, _vp, _vp, _vp, _vp]),
+                                    _vp, C.POINTER(_vp)]),
+    "slb_dev_stepper_step": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "slb_dev_stepper_destroy": (None, [_vp]),
     "slb_microbench_int": (_i, [_i, _i, _i, _vp, C.POINTER(_u64), _vp]),
 }
@@ -96,7 +97,7 @@ def load():
             fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
             fn.restype = res
             fn.argtypes = args
-        if lib.slb_abi_version() != 3:
+        if lib.slb_abi_version() != 4:
             raise ImportError("libsafelife_b200.so ABI version mismatch")
         _lib = lib
     return _lib

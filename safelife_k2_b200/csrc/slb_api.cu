@@ -242,40 +242,112 @@ int slb_advance_board(const uint16_t *d_in, uint16_t *d_out, int n, int h, int w
     return SLB_OK;
 }
 
+// Per-thread staging of slb_advance_board_host: a growable device block, a growable pinned (and therefore
+// device-mapped) host block and a non-blocking stream, all kept between calls — no allocation, no pageable
+// copy and no legacy-default-stream synchronisation per call.
+namespace {
+struct AdvStage {
+    int dev;
+    cudaStream_t st;
+    uint8_t *d, *h;
+    size_t dcap, hcap;
+};
+thread_local AdvStage g_adv = {-1, nullptr, nullptr, nullptr, 0, 0};
+constexpr size_t kAdvZeroCopyBytes = 64 * 1024;   // up to here the kernel reads / writes the pinned block itself
+constexpr size_t kAdvPinnedBytes = 256u << 20;    // larger batches are copied straight from / to the caller's arrays
+
+int adv_stage(size_t dbytes, size_t hbytes, AdvStage **out) {
+    int dev = 0;
+    SLB_CUDA(cudaGetDevice(&dev));
+    AdvStage *a = &g_adv;
+    if (a->dev != dev) {  // first use on this thread, or the thread moved to another device
+        if (a->st) { cudaStreamSynchronize(a->st); cudaStreamDestroy(a->st); }
+        if (a->d) cudaFree(a->d);
+        if (a->h) cudaFreeHost(a->h);
+        *a = AdvStage{dev, nullptr, nullptr, nullptr, 0, 0};
+        SLB_CUDA(cudaStreamCreateWithFlags(&a->st, cudaStreamNonBlocking));
+    }
+    if (dbytes > a->dcap) {
+        if (a->d) cudaFree(a->d);
+        a->d = nullptr; a->dcap = 0;
+        const size_t cap = dbytes + dbytes / 2;
+        SLB_CUDA(cudaMalloc(&a->d, cap));
+        a->dcap = cap;
+    }
+    if (hbytes > a->hcap) {
+        if (a->h) cudaFreeHost(a->h);
+        a->h = nullptr; a->hcap = 0;
+        const size_t cap = hbytes + hbytes / 2;
+        SLB_CUDA(cudaMallocHost(&a->h, cap));
+        a->hcap = cap;
+    }
+    *out = a;
+    return SLB_OK;
+}
+inline size_t up16(size_t x) { return (x + 15) & ~(size_t)15; }
+}  // namespace
+
 int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, int w,
                            const float *h_spawn_prob, uint64_t seed, uint64_t env_id0,
                            uint64_t *h_counters, int k_steps) {
     if (int rc = check_shape(n, h, w)) return rc;
     if (!h_in || !h_out || !h_spawn_prob) return fail(SLB_ERR_INVALID, "NULL host pointer");
+    if (k_steps < 1) return fail(SLB_ERR_INVALID, "k_steps must be >= 1");
     if (n == 0) return SLB_OK;
-    size_t cells = (size_t)n * h * w;
-    uint16_t *d_buf = nullptr;
-    float *d_p = nullptr;
-    uint64_t *d_c = nullptr;
-    cudaStream_t st = nullptr;
-    int rc = SLB_OK;
-    bool need_scratch = k_steps > 1 && !fast_shape(h, w);
-    SLB_CUDA(cudaMalloc(&d_buf, cells * 2 * (need_scratch ? 3 : 2)));
-    if (cudaMalloc(&d_p, (size_t)n * 4) != cudaSuccess || cudaMalloc(&d_c, (size_t)n * 8) != cudaSuccess) {
-        rc = fail(SLB_ERR_CUDA, "cudaMalloc failed");
-    } else {
-        cudaMemcpyAsync(d_buf, h_in, cells * 2, cudaMemcpyHostToDevice, st);
-        cudaMemcpyAsync(d_p, h_spawn_prob, (size_t)n * 4, cudaMemcpyHostToDevice, st);
-        if (h_counters) cudaMemcpyAsync(d_c, h_counters, (size_t)n * 8, cudaMemcpyHostToDevice, st);
-        else cudaMemsetAsync(d_c, 0, (size_t)n * 8, st);
-        rc = slb_advance_board(d_buf, d_buf + cells, n, h, w, d_p, seed, env_id0, d_c, k_steps,
-                               need_scratch ? d_buf + 2 * cells : nullptr, st);
-        if (rc == SLB_OK) {
-            cudaMemcpyAsync(h_out, d_buf + cells, cells * 2, cudaMemcpyDeviceToHost, st);
-            if (h_counters) cudaMemcpyAsync(h_counters, d_c, (size_t)n * 8, cudaMemcpyDeviceToHost, st);
-            cudaError_t e = cudaStreamSynchronize(st);
-            if (e != cudaSuccess) rc = fail(SLB_ERR_CUDA, "advance_board_host: %s", cudaGetErrorString(e));
-        }
+    const size_t cells = (size_t)n * h * w, bb = up16(cells * 2), pb = up16((size_t)n * 4), cb = up16((size_t)n * 8);
+    const bool need_scratch = k_steps > 1 && !fast_shape(h, w);
+    // block layout (host and device alike): [boards in | boards out | spawn_prob | counters | scratch]
+    const size_t o_out = bb, o_p = 2 * bb, o_c = o_p + pb, o_s = o_c + cb, total = o_s + (need_scratch ? bb : 0);
+    const bool zero_copy = 2 * bb <= kAdvZeroCopyBytes && !need_scratch;
+    const bool pinned = o_s <= kAdvPinnedBytes;
+    AdvStage *a = nullptr;
+    if (int rc = adv_stage(zero_copy ? 16 : total, pinned ? o_s : 16, &a)) return rc;
+    cudaStream_t st = a->st;
+    int rc;
+    if (zero_copy) {
+        // a few boards: the kernel reads the inputs from and writes the results to the pinned block over
+        // PCIe itself — one launch and one wait, no DMA copy
+        memcpy(a->h, h_in, cells * 2);
+        memcpy(a->h + o_p, h_spawn_prob, (size_t)n * 4);
+        if (h_counters) memcpy(a->h + o_c, h_counters, (size_t)n * 8);
+        else memset(a->h + o_c, 0, (size_t)n * 8);
+        rc = slb_advance_board((const uint16_t *)a->h, (uint16_t *)(a->h + o_out), n, h, w, (const float *)(a->h + o_p),
+                               seed, env_id0, (uint64_t *)(a->h + o_c), k_steps, nullptr, st);
+        if (rc != SLB_OK) return rc;
+        SLB_CUDA(cudaStreamSynchronize(st));
+        memcpy(h_out, a->h + o_out, cells * 2);
+        if (h_counters) memcpy(h_counters, a->h + o_c, (size_t)n * 8);
+        return SLB_OK;
     }
-    cudaFree(d_buf);
-    cudaFree(d_p);
-    cudaFree(d_c);
-    return rc;
+    const uint8_t *src_in = (const uint8_t *)h_in, *src_p = (const uint8_t *)h_spawn_prob;
+    if (pinned) {
+        memcpy(a->h, h_in, cells * 2);
+        memcpy(a->h + o_p, h_spawn_prob, (size_t)n * 4);
+        src_in = a->h; src_p = a->h + o_p;
+        if (h_counters) memcpy(a->h + o_c, h_counters, (size_t)n * 8);
+    }
+    SLB_CUDA(cudaMemcpyAsync(a->d, src_in, cells * 2, cudaMemcpyHostToDevice, st));
+    SLB_CUDA(cudaMemcpyAsync(a->d + o_p, src_p, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (h_counters)
+        SLB_CUDA(cudaMemcpyAsync(a->d + o_c, pinned ? (const void *)(a->h + o_c) : (const void *)h_counters,
+                                 (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    else
+        SLB_CUDA(cudaMemsetAsync(a->d + o_c, 0, (size_t)n * 8, st));
+    rc = slb_advance_board((const uint16_t *)a->d, (uint16_t *)(a->d + o_out), n, h, w, (const float *)(a->d + o_p),
+                           seed, env_id0, (uint64_t *)(a->d + o_c), k_steps,
+                           need_scratch ? (uint16_t *)(a->d + o_s) : nullptr, st);
+    if (rc != SLB_OK) return rc;
+    SLB_CUDA(cudaMemcpyAsync(pinned ? (void *)(a->h + o_out) : (void *)h_out, a->d + o_out, cells * 2,
+                             cudaMemcpyDeviceToHost, st));
+    if (h_counters)
+        SLB_CUDA(cudaMemcpyAsync(pinned ? (void *)(a->h + o_c) : (void *)h_counters, a->d + o_c, (size_t)n * 8,
+                                 cudaMemcpyDeviceToHost, st));
+    SLB_CUDA(cudaStreamSynchronize(st));
+    if (pinned) {
+        memcpy(h_out, a->h + o_out, cells * 2);
+        if (h_counters) memcpy(h_counters, a->h + o_c, (size_t)n * 8);
+    }
+    return SLB_OK;
 }
 
 #define RES_GRID(n) (((n) + RES_WARPS - 1) / RES_WARPS), RES_WARPS * 32, 0
@@ -297,6 +369,15 @@ int slb_env_reset(const slb_pool *pool, int n, const int32_t *d_level_ids, const
     } else
         reset_generic_kernel<<<n, GEN_THREADS, 0, (cudaStream_t)stream>>>(
             *pool, d_level_ids, d_mask, (uint16_t *)d_board, (uint16_t *)d_goals, d_state);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_env_set_min_performance(int n, slb_env_state *d_state, const uint8_t *d_mask, double value,
+                                void *stream) {
+    if (n < 0 || !d_state) return fail(SLB_ERR_INVALID, "slb_env_set_min_performance: bad arguments");
+    if (n == 0) return SLB_OK;
+    set_min_performance_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(n, d_state, d_mask, value);
     SLB_LAUNCHED();
     return SLB_OK;
 }
@@ -395,10 +476,10 @@ int slb_update_exit_colors(slb_pool *pool, int n, void *d_board, const void *d_g
     return SLB_OK;
 }
 
-int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
-                 slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
-                 uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
-                 void *stream) {
+static int env_step_impl(const slb_pool *pool, int n, void *d_board, void *d_goals,
+                         slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
+                         uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
+                         void *stream, unsigned long long *gc) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || !d_board || !d_goals || !d_state || !d_actions)
         return fail(SLB_ERR_INVALID, "slb_env_step: bad arguments");
@@ -408,10 +489,11 @@ int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
         if ((uint64_t)n * 16u * (uint64_t)pool->h >= (1ull << 32))
             return fail(SLB_ERR_UNSUPPORTED, "too many envs per launch (resident word offsets are 32-bit)");
         launch_res_env_rollout(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions, 1,
-                               time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, st);
+                               time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, st, gc);
         SLB_LAUNCHED();
         return SLB_OK;
     }
+    if (gc) return fail(SLB_ERR_UNSUPPORTED, "the in-kernel global counter needs boards of 4..32 rows / columns");
     if (big_shape(pool->h, pool->w)) {
         BigArgs a = big_args(n, d_board, d_goals, d_state, BIG_ACTION | BIG_PHYSICS | BIG_BOOK);
         a.actions = d_actions; a.time_limit = time_limit; a.seed = seed; a.env_id0 = env_id0;
@@ -430,6 +512,14 @@ int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
                                                           d_done, auto_reset_stride);
     SLB_LAUNCHED();
     return SLB_OK;
+}
+
+int slb_env_step(const slb_pool *pool, int n, void *d_board, void *d_goals,
+                 slb_env_state *d_state, const uint8_t *d_actions, int time_limit, uint64_t seed,
+                 uint64_t env_id0, int32_t *d_reward, uint8_t *d_done, int auto_reset_stride,
+                 void *stream) {
+    return env_step_impl(pool, n, d_board, d_goals, d_state, d_actions, time_limit, seed, env_id0, d_reward,
+                         d_done, auto_reset_stride, stream, nullptr);
 }
 
 int slb_env_rollout(const slb_pool *pool, int n, void *d_board, void *d_goals,
@@ -500,6 +590,8 @@ struct HostIo {
 thread_local HostIo g_slots[8] = {};
 thread_local int g_slots_used = 0;
 
+int finish_pending(HostIo *s);
+
 HostIo *find_slot(cudaStream_t st) {
     for (int k = 0; k < g_slots_used; k++)
         if (g_slots[k].st == st) return &g_slots[k];
@@ -532,6 +624,9 @@ int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
     static thread_local uint64_t use_clock = 0;
     s->last_use = ++use_clock;
     if (need > s->cap) {
+        // a step still in flight on this slot refers to the old blocks: deliver its outputs first
+        if (s->pend_n)
+            if (int rc = finish_pending(s)) return rc;
         SLB_CUDA(cudaStreamSynchronize(st));
         for (int k = 0; k < s->n_graphs; k++) cudaGraphExecDestroy(s->graphs[k].exec);
         s->n_graphs = 0;  // (graphs owned by steppers notice the new blocks and rebuild)
@@ -933,11 +1028,11 @@ int slb_get_obs_channels(const slb_pool *pool, int n, const void *d_board, const
     return slb_obs_channels(d_words_scratch, (size_t)n * vh * vw, h_channels, n_channels, d_out, stream);
 }
 
-int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
-                     const uint8_t *d_actions, int time_limit, uint64_t seed, uint64_t env_id0,
-                     int32_t *d_reward, uint8_t *d_done, int auto_reset_stride, int vh, int vw,
-                     int remove_white_goals, const uint8_t *h_channels, int n_channels, uint16_t *d_obs,
-                     void *stream) {
+static int env_step_obs_impl(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                             const uint8_t *d_actions, int time_limit, uint64_t seed, uint64_t env_id0,
+                             int32_t *d_reward, uint8_t *d_done, int auto_reset_stride, int vh, int vw,
+                             int remove_white_goals, const uint8_t *h_channels, int n_channels, uint16_t *d_obs,
+                             void *stream, unsigned long long *gc) {
     if (int rc = check_pool(pool)) return rc;
     if (n < 0 || vh < 1 || vw < 1 || !d_board || !d_goals || !d_state || !d_actions || !d_obs)
         return fail(SLB_ERR_INVALID, "slb_env_step_obs: bad arguments");
@@ -955,9 +1050,19 @@ int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, 
     oa.vh = vh; oa.vw = vw; oa.remove_white = remove_white_goals; oa.c_n = n_channels; oa.obs = d_obs;
     SLB_CUDA(launch_res_env_step_obs(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, d_actions,
                                      time_limit, seed, env_id0, d_reward, d_done, auto_reset_stride, oa, ident,
-                                     (cudaStream_t)stream));
+                                     (cudaStream_t)stream, gc));
     SLB_LAUNCHED();
     return SLB_OK;
+}
+
+int slb_env_step_obs(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
+                     const uint8_t *d_actions, int time_limit, uint64_t seed, uint64_t env_id0,
+                     int32_t *d_reward, uint8_t *d_done, int auto_reset_stride, int vh, int vw,
+                     int remove_white_goals, const uint8_t *h_channels, int n_channels, uint16_t *d_obs,
+                     void *stream) {
+    return env_step_obs_impl(pool, n, d_board, d_goals, d_state, d_actions, time_limit, seed, env_id0, d_reward,
+                             d_done, auto_reset_stride, vh, vw, remove_white_goals, h_channels, n_channels, d_obs,
+                             stream, nullptr);
 }
 
 // ---- device-buffer step with every per-batch argument bound once (the GPU-policy loop) -----------
@@ -970,35 +1075,61 @@ struct slb_dev_stepper {
     int32_t *reward;
     int vh, vw, remove_white, n_channels;  // vh == 0: no observation
     uint8_t channels[16];
+    unsigned long long *gc;  // SafeLifeEnv.global_counter on the device (may be NULL)
+    uint8_t *already;        // [n] scratch for the counter on shapes whose step kernel does not count
 };
 
 int slb_dev_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
                            int time_limit, uint64_t seed, uint64_t env_id0, int auto_reset_stride,
                            int32_t *d_reward, int vh, int vw, int remove_white_goals,
-                           const uint8_t *h_channels, int n_channels, slb_dev_stepper **out) {
+                           const uint8_t *h_channels, int n_channels, uint64_t *d_global_counter,
+                           slb_dev_stepper **out) {
     if (int rc = check_pool(pool)) return rc;
     if (!out || n < 0 || !d_board || !d_goals || !d_state || vh < 0 || vw < 0 || n_channels < 0 || n_channels > 16 ||
         (n_channels > 0 && !h_channels))
         return fail(SLB_ERR_INVALID, "slb_dev_stepper_create: bad arguments");
     slb_dev_stepper *s = new slb_dev_stepper{pool, n, time_limit, auto_reset_stride, d_board, d_goals, d_state,
-                                             seed, env_id0, d_reward, vh, vw, remove_white_goals, n_channels, {}};
+                                             seed, env_id0, d_reward, vh, vw, remove_white_goals, n_channels, {},
+                                             (unsigned long long *)d_global_counter, nullptr};
     for (int c = 0; c < n_channels; c++) s->channels[c] = h_channels[c];
+    if (d_global_counter && !fast_shape(pool->h, pool->w) && n > 0) {
+        if (cudaMalloc(&s->already, (size_t)n) != cudaSuccess) {
+            delete s;
+            return fail(SLB_ERR_CUDA, "slb_dev_stepper_create: cudaMalloc failed");
+        }
+    }
     *out = s;
     return SLB_OK;
 }
 
-int slb_dev_stepper_step(slb_dev_stepper *s, const uint8_t *d_actions, uint8_t *d_done, uint16_t *d_obs,
-                         void *stream) {
+int slb_dev_stepper_step(slb_dev_stepper *s, const uint8_t *d_actions, int32_t *d_reward, uint8_t *d_done,
+                         uint16_t *d_obs, void *stream) {
     if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
+    int32_t *reward = d_reward ? d_reward : s->reward;
     if (s->vh > 0 && d_obs)
-        return slb_env_step_obs(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
-                                s->env_id0, s->reward, d_done, s->stride, s->vh, s->vw, s->remove_white,
-                                s->n_channels ? s->channels : nullptr, s->n_channels, d_obs, stream);
-    return slb_env_step(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
-                        s->env_id0, s->reward, d_done, s->stride, stream);
+        return env_step_obs_impl(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
+                                 s->env_id0, reward, d_done, s->stride, s->vh, s->vw, s->remove_white,
+                                 s->n_channels ? s->channels : nullptr, s->n_channels, d_obs, stream, s->gc);
+    if (s->gc && s->already) {
+        // shapes whose step kernel does not count: who was already done, then the step, then the counts
+        if (!d_done) return fail(SLB_ERR_INVALID, "slb_dev_stepper_step: the global counter needs d_done");
+        gc_pre_kernel<<<(s->n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(s->n, s->state, s->already);
+        SLB_LAUNCHED();
+        if (int rc = env_step_impl(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
+                                   s->env_id0, reward, d_done, s->stride, stream, nullptr)) return rc;
+        gc_post_kernel<<<(s->n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(s->n, d_done, s->already, s->gc);
+        SLB_LAUNCHED();
+        return SLB_OK;
+    }
+    return env_step_impl(s->pool, s->n, s->board, s->goals, s->state, d_actions, s->time_limit, s->seed,
+                         s->env_id0, reward, d_done, s->stride, stream, s->gc);
 }
 
-void slb_dev_stepper_destroy(slb_dev_stepper *s) { delete s; }
+void slb_dev_stepper_destroy(slb_dev_stepper *s) {
+    if (!s) return;
+    if (s->already) cudaFree(s->already);
+    delete s;
+}
 
 int slb_obs_channels(const uint16_t *d_words, size_t m, const uint8_t *h_channels, int n_channels,
                      uint16_t *d_out, void *stream) {

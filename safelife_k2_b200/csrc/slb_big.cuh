@@ -570,6 +570,8 @@ __device__ inline void big_reset(const slb_pool &pool, int level, const BigGeo &
         st->game_over = 0; st->num_steps = 0; st->level_id = level; st->episode_length = 0;
         st->episode_completed = 0; st->old_points = pts; st->can_exit = ce; st->completed = completed;
         st->possible = possible; st->episode_reward = 0;
+        st->min_performance = pool.min_performance[level];  // deserialize (safelife_game.py:205)
+        st->flags = 0;
         // rng_counter deliberately untouched: the stream keeps running across episodes
     }
     __syncthreads();
@@ -631,7 +633,7 @@ big_env_kernel(slb_pool pool, BigArgs a) {
     big_score(board, goals, g, e0, false, scratch, pts, cur, pos);
     const int baseline = pool.baseline[level];
     const int completed = cur - baseline, possible = pos - baseline;
-    const int ce = can_exit_rule(pool.min_performance[level], completed, possible);
+    const int ce = can_exit_rule(st->min_performance, completed, possible);
     if (ops & BIG_POINTS) {
         if (threadIdx.x == 0) {
             if (a.points) a.points[i] = pts;
@@ -645,6 +647,7 @@ big_env_kernel(slb_pool pool, BigArgs a) {
     __shared__ int sh_done;
     if (threadIdx.x == 0) {
         st->can_exit = ce; st->completed = completed; st->possible = possible;
+        st->flags &= ~SLB_ENV_RESCORE;
         if (ops & BIG_BOOK) {
             const int reward = act_reward + pts - st->old_points;
             const int ep_len = st->episode_length + 1;

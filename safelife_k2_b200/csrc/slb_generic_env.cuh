@@ -48,7 +48,7 @@ env_step_generic_kernel(slb_pool pool, uint16_t *board, uint16_t *goals, slb_env
 
     const int baseline = pool.baseline[level];
     const int completed = cur - baseline, possible = pos - baseline;
-    const int ce = can_exit_rule(pool.min_performance[level], completed, possible);
+    const int ce = can_exit_rule(st->min_performance, completed, possible);
     // update_exit_colors: exit locations of the INITIAL board (safelife_game.py:528-537)
     const uint16_t *b0 = pool.board + (size_t)level * cells;
     const uint16_t exit_val = (uint16_t)(FROZEN | EXIT | (ce ? RED : 0u));
@@ -72,6 +72,7 @@ env_step_generic_kernel(slb_pool pool, uint16_t *board, uint16_t *goals, slb_env
         st->possible = possible;
         st->episode_reward += reward;
         st->rng_counter = counter;
+        st->flags = 0;  // this kernel re-scores and repaints every step
         if (reward_out) reward_out[i] = reward;
         if (done_out) done_out[i] = (uint8_t)done;
         sh_done = done;
@@ -210,6 +211,40 @@ penalty_generic_kernel(slb_pool pool, const uint16_t *__restrict__ board,
 
 // ---------------------------------------------------------------------------------------------
 // statistics for the all-reduce.  Single CTA loops over envs (n is small next to a step).
+// ---------------------------------------------------------------------------------------------
+// SafeLifeEnv.global_counter (safelife_env.py:169-173) around a step kernel that does not count itself:
+// who was done before the step, then (after it) num_steps += fresh, episodes_completed += done & fresh.
+__global__ void __launch_bounds__(256)
+gc_pre_kernel(int n, const slb_env_state *__restrict__ state, uint8_t *already) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) already[i] = (uint8_t)(state[i].episode_completed != 0);
+}
+
+__global__ void __launch_bounds__(256)
+gc_post_kernel(int n, const uint8_t *__restrict__ done, const uint8_t *__restrict__ already,
+               unsigned long long *gc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool fresh = i < n && !already[i];
+    const unsigned f = __ballot_sync(0xffffffffu, fresh), d = __ballot_sync(0xffffffffu, fresh && done[i]);
+    if ((threadIdx.x & 31) == 0) {
+        const int slot = (i >> 5) & 63;
+        if (f) atomicAdd(gc + 2 * slot, (unsigned long long)__popc(f));
+        if (d) atomicAdd(gc + 2 * slot + 1, (unsigned long long)__popc(d));
+    }
+}
+
+// `game.min_performance = value` from outside (env_wrappers.py:316): can_exit() re-evaluated from the
+// env's last performance_ratio(), exits repainted by the next step (SLB_ENV_RESCORE).
+__global__ void __launch_bounds__(256)
+set_min_performance_kernel(int n, slb_env_state *state, const uint8_t *__restrict__ mask, double value) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || (mask && !mask[i])) return;
+    slb_env_state *s = state + i;
+    s->min_performance = value;
+    s->can_exit = can_exit_rule(value, s->completed, s->possible);
+    s->flags |= SLB_ENV_RESCORE;
+}
+
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 stats_kernel(int n, const slb_env_state *__restrict__ state, const int32_t *__restrict__ reward,

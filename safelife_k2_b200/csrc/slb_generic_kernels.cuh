@@ -100,6 +100,8 @@ __device__ inline void reset_env_cta(const slb_pool &pool, int level, uint16_t *
         st->completed = completed;
         st->possible = possible;
         st->episode_reward = 0;
+        st->min_performance = pool.min_performance[level];  // deserialize (safelife_game.py:205)
+        st->flags = 0;
         // rng_counter deliberately untouched: the stream keeps running across episodes
     }
     __syncthreads();
@@ -153,8 +155,7 @@ points_generic_kernel(slb_pool pool, const uint16_t *__restrict__ board,
         if (completed) completed[i] = cur - baseline;
         if (possible) possible[i] = pos - baseline;
         if (can_exit)
-            can_exit[i] = (uint8_t)can_exit_rule(pool.min_performance[level], cur - baseline,
-                                                 pos - baseline);
+            can_exit[i] = (uint8_t)can_exit_rule(state[i].min_performance, cur - baseline, pos - baseline);
     }
 }
 
@@ -176,7 +177,7 @@ exit_colors_generic_kernel(slb_pool pool, uint16_t *board, const uint16_t *__res
     }
     block_sum3(pts, cur, pos, scratch);
     const int level = state[i].level_id, baseline = pool.baseline[level];
-    const int ce = can_exit_rule(pool.min_performance[level], cur - baseline, pos - baseline);
+    const int ce = can_exit_rule(state[i].min_performance, cur - baseline, pos - baseline);
     const uint16_t *b0 = pool.board + (size_t)level * cells;
     const uint16_t exit_val = (uint16_t)(FROZEN | EXIT | (ce ? RED : 0u));
     for (int c = threadIdx.x; c < cells; c += blockDim.x)
@@ -185,6 +186,7 @@ exit_colors_generic_kernel(slb_pool pool, uint16_t *board, const uint16_t *__res
         state[i].can_exit = ce;
         state[i].completed = cur - baseline;
         state[i].possible = pos - baseline;
+        state[i].flags &= ~SLB_ENV_RESCORE;
     }
 }
 

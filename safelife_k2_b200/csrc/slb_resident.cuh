@@ -70,24 +70,29 @@ __device__ __forceinline__ void store_res(uint32_t *__restrict__ base, const Geo
 }
 
 // ---------------------------------------------------------------------------------------------
-// Env scalars in registers (warp-uniform).  The 64-byte slb_env_state record moves as 4 x 16 B.
+// Env scalars in registers (warp-uniform).
 // ---------------------------------------------------------------------------------------------
 struct EnvRegs {
     int ax, ay, orientation, game_over, num_steps, level, ep_len, ep_done;
     int old_points, can_exit, completed, possible;
     long long ep_reward;
     uint64_t counter;
+    double min_perf;
+    uint32_t flags;
 };
 
+// The 80-byte slb_env_state record moves as 5 x 16 B.
 __device__ __forceinline__ EnvRegs load_env(const slb_env_state *s) {
     const uint4 *q = reinterpret_cast<const uint4 *>(s);
-    const uint4 a = q[0], b = q[1], c = q[2], d = q[3];
+    const uint4 a = q[0], b = q[1], c = q[2], d = q[3], f = q[4];
     EnvRegs e;
     e.ax = (int)a.x; e.ay = (int)a.y; e.orientation = (int)a.z; e.game_over = (int)a.w;
     e.num_steps = (int)b.x; e.level = (int)b.y; e.ep_len = (int)b.z; e.ep_done = (int)b.w;
     e.old_points = (int)c.x; e.can_exit = (int)c.y; e.completed = (int)c.z; e.possible = (int)c.w;
     e.ep_reward = (long long)(((uint64_t)d.y << 32) | d.x);
     e.counter = ((uint64_t)d.w << 32) | d.z;
+    e.min_perf = __hiloint2double((int)f.y, (int)f.x);
+    e.flags = f.z;
     return e;
 }
 
@@ -98,29 +103,32 @@ __device__ __forceinline__ void store_env(slb_env_state *s, const EnvRegs &e) {
     q[2] = make_uint4((uint32_t)e.old_points, (uint32_t)e.can_exit, (uint32_t)e.completed, (uint32_t)e.possible);
     q[3] = make_uint4((uint32_t)(uint64_t)e.ep_reward, (uint32_t)((uint64_t)e.ep_reward >> 32),
                       (uint32_t)e.counter, (uint32_t)(e.counter >> 32));
+    q[4] = make_uint4((uint32_t)__double2loint(e.min_perf), (uint32_t)__double2hiint(e.min_perf), e.flags, 0u);
 }
 
 struct LevelConsts {
     float spawn_prob;
     int baseline;
     uint32_t flags;
-    double min_perf;
     uint32_t e0;  // this lane's row of the level's initial exit cells
 };
 
-// pool.level_consts: one 32-byte slb_level_consts record per level, two 16-byte loads
+// pool.level_consts: one 32-byte slb_level_consts record per level; a step needs its first 16 bytes
+// (min_performance, the second half, is copied into the env's state by the reset)
 __device__ __forceinline__ LevelConsts load_level(const slb_pool &pool, int level, const Geo &g) {
     LevelConsts c;
     const int lane = threadIdx.x & 31;
-    const uint4 *rec = reinterpret_cast<const uint4 *>(pool.level_consts) + 2 * level;
-    const uint4 a = rec[0];
-    const uint2 b = *reinterpret_cast<const uint2 *>(rec + 1);
+    const uint4 a = reinterpret_cast<const uint4 *>(pool.level_consts)[2 * level];
     c.spawn_prob = __uint_as_float(a.x);
     c.baseline = (int)a.y;
     c.flags = pool.external_writes ? 0u : a.z;
-    c.min_perf = __hiloint2double((int)b.y, (int)b.x);
     c.e0 = g.row ? pool.exit_mask[level * g.h + lane] : 0u;
     return c;
+}
+
+__device__ __forceinline__ double load_level_min_perf(const slb_pool &pool, int level) {
+    const uint2 b = *reinterpret_cast<const uint2 *>(reinterpret_cast<const uint4 *>(pool.level_consts) + 2 * level + 1);
+    return __hiloint2double((int)b.y, (int)b.x);
 }
 
 // score -> completed / possible / can_exit (safelife_game.py:522-526, 601-631), then repaint the
@@ -132,8 +140,11 @@ __device__ __forceinline__ int score_and_paint(uint32_t B[16], const uint32_t G[
     const int pts = warp_sum(rs.points), cur = warp_sum(rs.current), pos = warp_sum(rs.possible);
     e.completed = cur - lc.baseline;
     e.possible = pos - lc.baseline;
-    e.can_exit = can_exit_rule(lc.min_perf, e.completed, e.possible);
-    if (paint) paint_exits(B, lc.e0, e.can_exit);
+    e.can_exit = can_exit_rule(e.min_perf, e.completed, e.possible);
+    if (paint) {
+        paint_exits(B, lc.e0, e.can_exit);
+        e.flags &= ~SLB_ENV_RESCORE;
+    }
     return pts;
 }
 
@@ -145,6 +156,8 @@ __device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, c
     load_res((const uint32_t *)pool.board_res + level * words, g, gb, B);
     load_res((const uint32_t *)pool.goals_res + level * words, g, gg, G);
     lc = load_level(pool, level, g);
+    e.min_perf = load_level_min_perf(pool, level);  // deserialize restores the level's value (safelife_game.py:205)
+    e.flags = 0;
     score_and_paint(B, G, g, lc, e, true);
     // _old_game_value is taken AFTER update_exit_colors (safelife_env.py:190-192): re-score, an
     // exit cell that was alive in the level record is dead once painted
@@ -157,11 +170,18 @@ __device__ __forceinline__ void reset_env_res(const slb_pool &pool, int level, c
 // One env step on the planes in registers (safelife_env.py:157-186): action, physics of board then
 // goals, reward, exit colours, counters, done.  Shared by the rollout kernel
 // and the fused step + observation kernel.  Returns the step's reward; `done` as the env reports it.
+// `gc` (may be NULL): SafeLifeEnv.global_counter on the device (safelife_env.py:169-173), GC_SLOTS pairs
+// {num_steps, episodes_completed}; env i adds to pair i % GC_SLOTS so that the adds of one launch spread over
+// GC_SLOTS addresses (fire-and-forget reductions; the host sums the pairs when it reads the counter).
+constexpr int GC_SLOTS = 64;
+
 template <unsigned GB, unsigned GG>
 __device__ __forceinline__ int env_step_once(const slb_pool &pool, const Geo &g, uint32_t B[16], uint32_t G[16],
                                              LevelConsts &lc, EnvRegs &e, int action, uint64_t seed, uint64_t env,
-                                             int time_limit, bool &g_dirty, int &done) {
+                                             int time_limit, bool &g_dirty, int &done,
+                                             unsigned long long *gc = nullptr, int slot = 0) {
     bool touched, life_touched, ch_b, ch_g = false;
+    const int already = e.ep_done;
     int reward = action_planes(B, g, e.ax, e.ay, e.orientation, e.game_over, action, e.can_exit, touched,
                                life_touched);
     // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
@@ -174,7 +194,7 @@ __device__ __forceinline__ int env_step_once(const slb_pool &pool, const Geo &g,
     // the action moved no living cell and neither board changed, points, completed, possible
     // and can_exit are what they were, and the exit cells (frozen, never overwritten by an
     // action) still carry the colour painted for that can_exit.
-    if (life_touched || ch_b || ch_g || pool.external_writes) {
+    if (life_touched || ch_b || ch_g || pool.external_writes || (e.flags & SLB_ENV_RESCORE)) {
         const int pts = score_and_paint(B, G, g, lc, e, true);
         reward += pts - e.old_points;
         e.old_points = pts;
@@ -183,6 +203,10 @@ __device__ __forceinline__ int env_step_once(const slb_pool &pool, const Geo &g,
     e.ep_reward += reward;
     done = (e.ep_len > time_limit) || e.game_over;
     e.ep_done = done;
+    if (gc && !already && (threadIdx.x & 31) == 0) {  // only until the first done (safelife_env.py:169)
+        atomicAdd(gc + 2 * (slot & (GC_SLOTS - 1)), 1ull);
+        if (done) atomicAdd(gc + 2 * (slot & (GC_SLOTS - 1)) + 1, 1ull);
+    }
     return reward;
 }
 
@@ -199,7 +223,7 @@ __global__ void __launch_bounds__(RES_WARPS * 32, SLB_RES_SLOTS / RES_WARPS)
 res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                        const uint8_t *__restrict__ actions, int t_steps, int time_limit,
                        uint64_t seed, uint64_t env_id0, int32_t *reward_out, uint8_t *done_out,
-                       int auto_reset_stride, int l2_prefetch) {
+                       int auto_reset_stride, int l2_prefetch, unsigned long long *gc) {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
     // Programmatic dependent launch: let the next kernel on the stream begin launching now (its CTAs
@@ -217,7 +241,7 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
         const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
         if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)bp + lane * 128));
         if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)gp + lane * 128));
-        if (lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(state + i));
+        if (lane >= 30) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(state + i) + (lane - 30) * 64));
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
@@ -238,7 +262,7 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
         int next_action = 0;
         if (!ONE && t + 1 < steps) next_action = actions[(size_t)(t + 1) * n + i];
         int done;
-        const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done);
+        const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done, gc, i);
         if (lane == 0) {
             const size_t o = ONE ? 0 : (size_t)t * n + i;
             if (reward_out) reward_out[o] = reward;
@@ -259,7 +283,8 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
 inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board, uint32_t *goals,
                                    slb_env_state *state, const uint8_t *actions, int t_steps,
                                    int time_limit, uint64_t seed, uint64_t env0, int32_t *reward,
-                                   uint8_t *done, int stride, cudaStream_t st) {
+                                   uint8_t *done, int stride, cudaStream_t st,
+                                   unsigned long long *gc = nullptr) {
     const int grid = (n + RES_WARPS - 1) / RES_WARPS;
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     // launched with programmatic stream serialization (see the griddepcontrol pair in the kernel)
@@ -279,7 +304,7 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
 #define SLB_ROLL3(GBV, GGV, HWV, ONEV)                                                               \
     cudaLaunchKernelEx(&cfg, res_env_rollout_kernel<GBV, GGV, HWV, ONEV>, pool, n, board, goals,      \
                        state, actions, t_steps, time_limit, seed, env0, reward, done, stride,         \
-                       l2_prefetch)
+                       l2_prefetch, gc)
 #define SLB_ROLL2(GBV, GGV, HWV)                                                                     \
     do {                                                                                             \
         if (t_steps == 1) SLB_ROLL3(GBV, GGV, HWV, true);                                            \
@@ -378,6 +403,7 @@ res_env_step_host_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals,
         __syncthreads();
         if (threadIdx.x == 0) {
             *ht.counter = 0;
+            __threadfence_system();  // release: every thread's stores (fenced above) before the sequence number
             *reinterpret_cast<volatile uint32_t *>(ht.h_seq) = ht.seq;
         }
     }
@@ -801,7 +827,7 @@ __global__ void __launch_bounds__(RES_WARPS * 32, SLB_RES_SLOTS / RES_WARPS)
 res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                         const uint8_t *__restrict__ actions, int time_limit, uint64_t seed, uint64_t env_id0,
                         int32_t *reward_out, uint8_t *done_out, int auto_reset_stride, int l2_prefetch,
-                        ObsArgs oa) {
+                        ObsArgs oa, unsigned long long *gc) {
     __shared__ __align__(16) uint16_t stage[RES_WARPS][RES_STAGE_U16];
     __shared__ __align__(16) uint16_t view_sm[CHANNELS ? RES_WARPS : 1][CHANNELS ? RES_VIEW_ROW : 8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -816,7 +842,7 @@ res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, 
         const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
         if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)bp + lane * 128));
         if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)gp + lane * 128));
-        if (lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(state + i));
+        if (lane >= 30) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(state + i) + (lane - 30) * 64));
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     EnvRegs e = load_env(state + i);
@@ -827,7 +853,7 @@ res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, 
     const uint64_t env = env_id0 + (uint64_t)i;
     bool g_dirty = false;
     int done;
-    const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done);
+    const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done, gc, i);
     if (lane == 0) {
         if (reward_out) reward_out[i] = reward;
         if (done_out) done_out[i] = (uint8_t)done;
@@ -846,7 +872,8 @@ res_env_step_obs_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, 
 inline cudaError_t launch_res_env_step_obs(const slb_pool &pool, int n, uint32_t *board, uint32_t *goals,
                                            slb_env_state *state, const uint8_t *actions, int time_limit,
                                            uint64_t seed, uint64_t env0, int32_t *reward, uint8_t *done, int stride,
-                                           const ObsArgs &oa, bool ident, cudaStream_t st) {
+                                           const ObsArgs &oa, bool ident, cudaStream_t st,
+                                           unsigned long long *gc = nullptr) {
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     static const bool pdl = []() { const char *v = getenv("SLB_PDL"); return !v || v[0] != '0'; }();
     static const bool pf = []() { const char *v = getenv("SLB_L2_PREFETCH"); return !v || v[0] != '0'; }();
@@ -863,7 +890,7 @@ inline cudaError_t launch_res_env_step_obs(const slb_pool &pool, int n, uint32_t
     const bool chan = oa.c_n > 0;
 #define SLB_SO3(GBV, GGV, HWV, CH, ID)                                                                        \
     return cudaLaunchKernelEx(&cfg, res_env_step_obs_kernel<GBV, GGV, HWV, CH, ID>, pool, n, board, goals,     \
-                              state, actions, time_limit, seed, env0, reward, done, stride, l2_prefetch, oa)
+                              state, actions, time_limit, seed, env0, reward, done, stride, l2_prefetch, oa, gc)
 #define SLB_SO2(GBV, GGV, HWV)                                                                                \
     do {                                                                                                      \
         if (!chan) SLB_SO3(GBV, GGV, HWV, false, true);                                                       \

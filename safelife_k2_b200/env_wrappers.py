@@ -35,9 +35,10 @@ class BaseWrapper(object):
         return getattr(self.env, name)
 
     def scheduled(self, val):
+        if not callable(val):
+            return val  # (the counter is only read — one device sync with a GlobalCounter — for a schedule)
         counter = self.global_counter
-        num_steps = 0 if counter is None else counter.num_steps
-        return val(num_steps) if callable(val) else val
+        return val(0 if counter is None else counter.num_steps)
 
     def step(self, action):
         return self.env.step(action)
@@ -122,8 +123,9 @@ class SimpleSideEffectPenalty(BaseWrapper):
             self.last_side_effect = torch.zeros(g.n, dtype=torch.int32, device=g.pool.device)
         else:
             self.last_side_effect = torch.where(m, torch.zeros_like(self.last_side_effect), self.last_side_effect)
-        # `self.game.min_performance = ...` (:314): every level of the pool gets the scheduled value
-        g.pool.min_performance.fill_(float(self.scheduled(self.min_performance)))
+        # `self.game.min_performance = ...` (:316) for the envs that were just reset: per-env game state,
+        # the envs that are in the middle of an episode keep the value scheduled at their own reset
+        g.set_min_performance(float(self.scheduled(self.min_performance)), None if mask is None else m)
         return obs
 
     def side_effect_count(self):

@@ -9,8 +9,6 @@ execute_action -> advance_board (board, goals) -> current_points -> reward -> up
 Keyword parameters keep the reference names: time_limit, remove_white_goals, view_shape,
 output_channels, global_counter (safelife_env.py:73-95).
 """
-from types import SimpleNamespace
-
 import os
 
 import numpy as np
@@ -97,6 +95,68 @@ class _Info(dict):
         return key in self._KEYS or super().__contains__(key)
 
 
+class GlobalCounter(object):
+    """SafeLifeEnv.global_counter (safelife_env.py:81-85: episodes_started, episodes_completed, num_steps)
+    without a host synchronisation per step: every env batch that uses the counter owns a small device
+    buffer that its step kernel adds to (slb_dev_stepper_create's d_global_counter), and the attributes are
+    summed up when they are READ (one device->host copy per batch then).  Assigning to an attribute works
+    (`counter.num_steps = 0`).  Like the reference's class-level SimpleNamespace, one GlobalCounter is the
+    class-level default and is shared by every SafeLifeEnv that is not given its own."""
+
+    def __init__(self, episodes_started=0, episodes_completed=0, num_steps=0):
+        object.__setattr__(self, "_base", {"episodes_started": int(episodes_started),
+                                            "episodes_completed": int(episodes_completed),
+                                            "num_steps": int(num_steps)})
+        object.__setattr__(self, "_sources", [])  # weak references to the envs' device buffers
+
+    def _register(self, buf):
+        import weakref
+        self._sources.append(weakref.ref(buf))
+
+    def _device_sums(self):
+        steps = done = 0
+        alive = []
+        for r in self._sources:
+            buf = r()
+            if buf is None:
+                continue
+            alive.append(r)
+            v = buf.cpu().view(-1, 2).sum(0)
+            steps += int(v[0])
+            done += int(v[1])
+        self._sources[:] = alive
+        return steps, done
+
+    def _retire(self, buf):
+        """fold a device buffer that is going away into the host totals"""
+        v = buf.cpu().view(-1, 2).sum(0)
+        self._base["num_steps"] += int(v[0])
+        self._base["episodes_completed"] += int(v[1])
+        self._sources[:] = [r for r in self._sources if r() is not None and r() is not buf]
+
+    def __getattr__(self, name):
+        base = object.__getattribute__(self, "_base")
+        if name not in base:
+            raise AttributeError(name)
+        if name == "episodes_started":
+            return base[name]
+        steps, done = self._device_sums()
+        return base[name] + (steps if name == "num_steps" else done)
+
+    def __setattr__(self, name, value):
+        if name not in self._base:
+            raise AttributeError(name)
+        if name == "episodes_started":
+            self._base[name] = int(value)
+            return
+        steps, done = self._device_sums()
+        self._base[name] = int(value) - (steps if name == "num_steps" else done)
+
+    def __repr__(self):
+        return "GlobalCounter(episodes_started=%d, episodes_completed=%d, num_steps=%d)" % (
+            self.episodes_started, self.episodes_completed, self.num_steps)
+
+
 class SafeLifeEnv(object):
     metadata = {"render.modes": []}
     action_names = ACTION_NAMES
@@ -106,7 +166,7 @@ class SafeLifeEnv(object):
     remove_white_goals = True
     view_shape = (15, 15)
     output_channels = tuple(range(15))
-    global_counter = SimpleNamespace(episodes_started=0, episodes_completed=0, num_steps=0)
+    global_counter = GlobalCounter()  # any other object with the three attributes is updated eagerly (two syncs per step)
 
     # batched-only knobs
     num_envs = 1
@@ -134,6 +194,10 @@ class SafeLifeEnv(object):
         self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
         dev = self.pool.device
         self._reward = torch.zeros(self.num_envs, dtype=torch.int32, device=dev)
+        self._gc_dev = None
+        if isinstance(self.global_counter, GlobalCounter):
+            self._gc_dev = torch.zeros(128, dtype=torch.int64, device=dev)  # 64 x {num_steps, episodes_completed}
+            self.global_counter._register(self._gc_dev)
         self._done = torch.zeros(self.num_envs, dtype=torch.uint8, device=dev)
         if self.level_ids is None:
             self._next_level = (np.arange(self.num_envs) + self.env_id0) % self.pool.n_levels
@@ -212,9 +276,12 @@ class SafeLifeEnv(object):
         return self._ch
 
     def step(self, action):
-        """action: int array/tensor [N] (0..8).  Returns (obs, reward int32 [N], done bool [N], info).
+        """action: int array/tensor [N] (0..8).  Returns (obs, reward int32 [N], done bool [N], info); the
+        reference's reward is a numpy.int64 scalar, here an int32 tensor (|reward| <= 5 * H * W).  reward and
+        done are fresh tensors every step (a rollout buffer may keep them).
         The call path is kept short for a policy on the GPU: a contiguous uint8 cuda tensor of actions is
-        used as it is, `done` is a bool view of the step's uint8 output, `info` is filled on access."""
+        used as it is, `done` is a bool view of the step's uint8 output, `info` is filled on access, and the
+        default global_counter (a GlobalCounter) is counted by the step kernel itself."""
         g = self.game
         assert g is not None, "Game state is not initialized."
         if (type(action) is torch.Tensor and action.dtype == torch.uint8 and action.is_cuda
@@ -222,37 +289,40 @@ class SafeLifeEnv(object):
             acts = action
         else:
             acts = g._actions(action)
-        already = g._field("episode_completed").clone() if self.global_counter is not None else None
+        eager = self.global_counter is not None and self._gc_dev is None
+        already = g._field("episode_completed").clone() if eager else None
         if torch.cuda.current_device() != self._dev_index:
             torch.cuda.set_device(self._dev_index)
         st = torch.cuda.current_stream().cuda_stream
         # every argument that does not change from step to step is bound once in a native stepper
         oc = self.output_channels
         key = (id(g), self.time_limit, g.seed, self.auto_reset, self.view_shape, tuple(oc) if oc else None,
-               self.remove_white_goals, self.compute_obs, self._fused_obs)
+               self.remove_white_goals, self.compute_obs, self._fused_obs, self.global_counter is not None)
         if key != self._dev_key:
             self._bind_dev_stepper(key)
         dev = self.pool.device
         done = torch.empty(g.n, dtype=torch.bool, device=dev)  # the step writes 0 / 1; fresh every step
-        self._done = done.view(torch.uint8)
+        reward = torch.empty(g.n, dtype=torch.int32, device=dev)
+        self._done, self._reward = done.view(torch.uint8), reward
         obs = torch.empty(self._obs_shape, dtype=torch.uint16, device=dev) if self._obs_shape is not None else None
-        rc = self._dev_step(self._dev_sp, acts.data_ptr(), done.data_ptr(), obs.data_ptr() if obs is not None else None, st)
+        rc = self._dev_step(self._dev_sp, acts.data_ptr(), reward.data_ptr(), done.data_ptr(),
+                            obs.data_ptr() if obs is not None else None, st)
         if rc == _lib.SLB_ERR_UNSUPPORTED and obs is not None:
             # this board / view shape has no fused step + observation: step, then get_obs
             self._fused_obs = False
-            self._bind_dev_stepper(key[:-1] + (False,))
+            self._bind_dev_stepper(key[:8] + (False,) + key[9:])
             obs = None
-            rc = self._dev_step(self._dev_sp, acts.data_ptr(), done.data_ptr(), None, st)
+            rc = self._dev_step(self._dev_sp, acts.data_ptr(), reward.data_ptr(), done.data_ptr(), None, st)
         if rc:
             _lib.check(rc)
-        if self.global_counter is not None:
+        if eager:
             fresh = already == 0
             self.global_counter.episodes_completed += int((done & fresh).sum().item())
             self.global_counter.num_steps += int(fresh.sum().item())
         info = _Info(g, self.time_limit)
         if obs is None and self.compute_obs:
             obs = self.get_obs()
-        return obs, self._reward, done, info
+        return obs, reward, done, info
 
     def _bind_dev_stepper(self, key):
         import ctypes
@@ -271,7 +341,9 @@ class SafeLifeEnv(object):
             self.pool.c, g.n, g.board_res.data_ptr(), g.goals_res.data_ptr(), g.state.data_ptr(),
             int(self.time_limit), g.seed, g.env_id0, self._stride() if self.auto_reset else 0,
             self._reward.data_ptr(), vh, vw, int(self.remove_white_goals),
-            ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0, ctypes.byref(out)))
+            ch.ctypes.data if ch is not None else None, ch.size if ch is not None else 0,
+            self._gc_dev.data_ptr() if (self._gc_dev is not None and self.global_counter is not None) else None,
+            ctypes.byref(out)))
         self._dev_sp, self._dev_key, self._dev_step = out, key, self._lib.slb_dev_stepper_step
 
     def step_host(self, actions_host, reward_host, done_host, sync=True, stream=None):

@@ -73,9 +73,11 @@ ENV_STATE_DTYPE = np.dtype([
     ("num_steps", "<i4"), ("level_id", "<i4"), ("episode_length", "<i4"),
     ("episode_completed", "<i4"), ("old_points", "<i4"), ("can_exit", "<i4"),
     ("completed", "<i4"), ("possible", "<i4"), ("episode_reward", "<i8"), ("rng_counter", "<u8"),
+    ("min_performance", "<f8"), ("flags", "<u4"), ("reserved", "<u4"),
 ])
-assert ENV_STATE_DTYPE.itemsize == 64
-# int32 column index of each field in the [N,16] int32 view of the state tensor
+assert ENV_STATE_DTYPE.itemsize == 80
+STATE_WORDS = ENV_STATE_DTYPE.itemsize // 4
+# int32 column index of each field in the [N,20] int32 view of the state tensor
 _COL = {name: ENV_STATE_DTYPE.fields[name][1] // 4 for name in ENV_STATE_DTYPE.names}
 
 
@@ -223,7 +225,7 @@ class SafeLifeGame(object):
     board, goals : uint16 [N,H,W] cuda tensors — materialised on access from the RESIDENT state
                    (board_res / goals_res, the bit-sliced layout the kernels compute in; see
                    include/safelife_b200.h); assigning to them imports the cells
-    state        : int32 [N,16] cuda tensor (slb_env_state records)
+    state        : int32 [N,20] cuda tensor (80-byte slb_env_state records)
     """
 
     points_on_level_exit = +1  # safelife_game.py:163
@@ -235,7 +237,7 @@ class SafeLifeGame(object):
         dev = pool.device
         self.board_res = torch.zeros(self.n * pool.resident_bytes, dtype=torch.uint8, device=dev)
         self.goals_res = torch.zeros_like(self.board_res)
-        self.state = torch.zeros((self.n, 16), dtype=torch.int32, device=dev)
+        self.state = torch.zeros((self.n, STATE_WORDS), dtype=torch.int32, device=dev)
         self._lib = _lib.load()
         if level_ids is None:
             level_ids = np.arange(self.n) % pool.n_levels
@@ -248,6 +250,8 @@ class SafeLifeGame(object):
     def _field(self, name):
         if name == "episode_reward" or name == "rng_counter":
             return self.state.view(torch.int64)[:, _COL[name] // 2]
+        if name == "min_performance":
+            return self.state.view(torch.float64)[:, _COL[name] // 2]
         return self.state[:, _COL[name]]
 
     def state_numpy(self):
@@ -336,7 +340,24 @@ class SafeLifeGame(object):
 
     @property
     def min_performance(self):
-        return self.pool.min_performance[self.level_id.long()]
+        """GameState.min_performance (safelife_game.py:166) per env: the level's value after a reset
+        (deserialize, :205) until something assigns to it."""
+        return self._field("min_performance")
+
+    @min_performance.setter
+    def min_performance(self, value):
+        self.set_min_performance(value)
+
+    def set_min_performance(self, value, mask=None):
+        """``game.min_performance = value`` for every env (or the envs in `mask`): can_exit() sees it from the
+        next execute_action on and the exits are repainted by the next step, like the reference's
+        update_exit_colors (slb_env_set_min_performance)."""
+        m = None
+        if mask is not None:
+            m = torch.as_tensor(mask).to(self.pool.device).to(torch.uint8).contiguous()
+        with torch.cuda.device(self.pool.device):
+            _lib.check(self._lib.slb_env_set_min_performance(self.n, self.state.data_ptr(), _lib.ptr(m),
+                                                             float(value), self._s()))
 
     # -- reference methods ------------------------------------------------------------------
     def revert(self, level_ids=None, mask=None):

@@ -23,12 +23,26 @@ CAN_OSCILLATE_MASK = 2
 INCLUDE_VIOLATIONS_MASK = 4
 
 _stream = {"seed": 0, "env": 0, "counter": 0}
+# draw counters of the boards of a batch (board i of a batch call consumes env i's stream, and like the
+# reference's global stream it keeps consuming over successive calls): a host array for ndarray batches, one
+# device tensor per device for tensor batches; both grow with the largest batch seen and rewind at seed()
+_batch = {"host": np.zeros(0, dtype=np.uint64), "dev": {}}
 
 
 def seed(i):
     """speedups.seed (module.c:246-253): reseed and flush."""
     _stream["seed"] = int(i) & 0xFFFFFFFF
     _stream["counter"] = 0
+    _batch["host"] = np.zeros(0, dtype=np.uint64)
+    _batch["dev"] = {}
+
+
+def _host_counters(n):
+    c = _batch["host"]
+    if c.size < n:
+        c = np.concatenate([c, np.zeros(n - c.size, dtype=np.uint64)])
+        _batch["host"] = c
+    return c
 
 
 def advance_board(board, spawn_prob=0.3):
@@ -37,7 +51,8 @@ def advance_board(board, spawn_prob=0.3):
     CUDA uint16/int16 torch tensor (then the result is a CUDA tensor and nothing leaves the GPU).
 
     A single board draws from the module stream (see ``seed``).  In a batch, board i draws from
-    its own stream (env id i) starting at draw 0.
+    its own stream (env id i); successive calls keep consuming those streams (``seed`` rewinds them),
+    so ``for _ in range(k): b = advance_board(b)`` sees fresh draws every step like the reference.
     """
     if hasattr(board, "is_cuda"):
         return _advance_tensor(board, spawn_prob)
@@ -58,8 +73,9 @@ def advance_board(board, spawn_prob=0.3):
         n, h, w = b.shape
         out = np.empty_like(b)
         p = np.broadcast_to(np.asarray(spawn_prob, dtype=np.float32), (n,)).copy()
+        ctr = _host_counters(n)  # (a view of the first n entries is contiguous)
         _lib.check(_lib.load().slb_advance_board_host(b.ctypes.data, out.ctypes.data, n, h, w,
-                                                      p.ctypes.data, _stream["seed"], 0, None, 1))
+                                                      p.ctypes.data, _stream["seed"], 0, ctr.ctypes.data, 1))
         return out
     raise ValueError("board must be a non-empty [H,W] or [N,H,W] array")
 
@@ -76,9 +92,15 @@ def _advance_tensor(board, spawn_prob):
     n, h, w = b.shape
     out = torch.empty_like(b)
     p = torch.as_tensor(spawn_prob, dtype=torch.float32, device=b.device).expand(n).contiguous()
-    ctr = None
     if single:
         ctr = torch.tensor([_stream["counter"]], dtype=torch.int64, device=b.device)
+    else:
+        ctr = _batch["dev"].get(b.device)
+        if ctr is None or ctr.numel() < n:
+            grown = torch.zeros(n, dtype=torch.int64, device=b.device)
+            if ctr is not None:
+                grown[:ctr.numel()] = ctr
+            ctr = _batch["dev"][b.device] = grown
     with torch.cuda.device(b.device):
         _lib.check(_lib.load().slb_advance_board(b.data_ptr(), out.data_ptr(), n, h, w, p.data_ptr(),
                                                  _stream["seed"], _stream["env"] if single else 0,

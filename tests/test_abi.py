@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "libsafelife_b200.so does not export %s" % n
     assert sorted(_lib.SYMBOLS) == names, "python binding table out of sync with the header"
-    assert _lib.load().slb_abi_version() == 3
+    assert _lib.load().slb_abi_version() == 4
 
 
 def test_env_state_layout_matches_header():
@@ -34,10 +34,10 @@ def test_env_state_layout_matches_header():
     src = open(HEADER).read()
     body = src[src.index("typedef struct {", src.index("Per-env scalar state")):src.index("} slb_env_state;")]
     fields = []
-    for ctype, names in re.findall(r"\b(int32_t|int64_t|uint64_t)\s+([a-z_, ]+);", body):
+    for ctype, names in re.findall(r"\b(int32_t|int64_t|uint64_t|uint32_t|double)\s+([a-z_, ]+);", body):
         fields += [n.strip() for n in names.split(",")]
     assert fields == list(ENV_STATE_DTYPE.names) == list(ORACLE_DTYPE.names)
-    assert ENV_STATE_DTYPE.itemsize == 64
+    assert ENV_STATE_DTYPE.itemsize == 80
 
 
 def test_argument_checks_without_gpu():
@@ -59,9 +59,9 @@ def test_argument_checks_without_gpu():
     assert L.slb_stepper_create(None, 1, a, a, a, 1000, 0, 0, 0, None, ctypes.byref(out)) == _lib.SLB_ERR_INVALID
     assert L.slb_stepper_step(None, a, a, a) == _lib.SLB_ERR_INVALID
     assert L.slb_stepper_wait(None) == _lib.SLB_ERR_INVALID
-    assert L.slb_dev_stepper_create(None, 1, a, a, a, 1000, 0, 0, 0, a, 15, 15, 1, None, 0, ctypes.byref(out)) \
+    assert L.slb_dev_stepper_create(None, 1, a, a, a, 1000, 0, 0, 0, a, 15, 15, 1, None, 0, None, ctypes.byref(out)) \
         == _lib.SLB_ERR_INVALID
-    assert L.slb_dev_stepper_step(None, a, a, a, None) == _lib.SLB_ERR_INVALID
+    assert L.slb_dev_stepper_step(None, a, a, a, a, None) == _lib.SLB_ERR_INVALID
     assert L.slb_microbench_int(2, 1, 1, a, None, None) == _lib.SLB_ERR_INVALID
     assert L.slb_microbench_int(0, 0, 1, a, None, None) == _lib.SLB_ERR_INVALID
 
