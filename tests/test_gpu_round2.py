@@ -1,0 +1,276 @@
+"""GPU parity tests added in round 2: the wrapper's per-env min_performance, the device-side global counter,
+speedups batch streams, the host advance_board staging paths, the 256x256 fused step at length, and a bounded
+soak over every archive (what scripts/soak_*.py cover, sized for the suite).  Bit-exact throughout."""
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import slo
+from tests import golden_util as gu
+from tests.test_gpu_parity import _random_levels, sl  # noqa: F401  (fixture)
+
+pytestmark = pytest.mark.gpu
+
+
+def _exit_level(h, w, p=2):
+    """agent at (2,2) facing right, exit right of it, one blue goal cell so that `possible` = 1 and `completed`
+    = 0; the level file says min_performance = -1 (exit open)"""
+    board = np.zeros((p, h, w), np.uint16)
+    board[:, 2, 2] = 122
+    board[:, 2, 3] = 272
+    goals = np.zeros_like(board)
+    goals[:, h - 1, w - 1] = 2048
+    return {"board": board, "goals": goals, "agent_loc": np.tile([2, 2], (p, 1)), "orientation": np.ones(p, int),
+            "spawn_prob": np.full(p, 0.3), "min_performance": np.full(p, -1.0)}
+
+
+@pytest.mark.parametrize("h,w", [(26, 26), (6, 6), (6, 40), (8, 64)])
+def test_wrapper_min_performance_reaches_can_exit(sl, h, w):
+    """SimpleSideEffectPenalty.reset sets game.min_performance AFTER env.reset (env_wrappers.py:313-317): the
+    exit was painted with the level's value, the next execute_action and update_exit_colors use the wrapper's.
+    Warp-per-env (26x26, 6x6), generic (6x40) and CTA-per-env (8x64) kernels, vs the oracle and by hand."""
+    from safelife_k2_b200 import env_wrappers as ew
+
+    lv = _exit_level(h, w)
+    n = 4
+    pool = sl.game.LevelPool(lv)
+    env = ew.SimpleSideEffectPenalty(
+        sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False), min_performance=0.3)
+    env.seed(0)
+    env.reset()
+    o = slo.OracleBatchEnv(slo.OraclePool(**lv), np.arange(n) % 2, seed=0)
+    o.states["min_performance"][:] = 0.3  # what the reference wrapper assigns after the reset
+    g = env.game
+    assert (g.board.cpu().numpy() == o.boards).all()
+    assert (g.board.cpu().numpy()[:, 2, 3] == 784).all()      # painted red by the reset (level value -1)
+    assert g.min_performance.cpu().tolist() == [0.3] * n
+    rng = np.random.RandomState(1)
+    for t in range(8):
+        acts = np.full(n, 2) if t == 0 else rng.randint(9, size=n)  # first: MOVE RIGHT into the exit
+        _, r, d, _ = env.step(acts)
+        orr, od = o.step(acts)
+        assert (d.cpu().numpy() == (od != 0)).all(), t
+        assert (g.board.cpu().numpy() == o.boards).all(), t
+        st = g.state_numpy()
+        for f in st.dtype.names:
+            assert (st[f] == o.states[f]).all(), (f, t)
+        if t == 0:
+            assert not d.any() and (st["game_over"] == 0).all()      # the exit is closed at 30 %
+            assert (g.board.cpu().numpy()[:, 2, 3] == 272).all()      # and no longer red
+    # per-env: a masked reset only gives the scheduled value to the envs it resets
+    env.min_performance = -1.0
+    env.reset(np.array([True, False, False, True]))
+    assert g.min_performance.cpu().tolist() == [-1.0, 0.3, 0.3, -1.0]
+    _, r, d, _ = env.step(np.full(n, 2))
+    st = g.state_numpy()
+    assert st["game_over"][0] == 1 and st["game_over"][3] == 1 and d[0] and d[3]
+
+
+@pytest.mark.parametrize("h,w,auto", [(26, 26, True), (26, 26, False), (9, 40, True), (8, 64, False)])
+def test_global_counter_on_device(sl, h, w, auto):
+    """The default GlobalCounter (counted by the step kernel / two small kernels, read lazily) equals the eager
+    host count of safelife_env.py:169-173."""
+    rng = np.random.RandomState(7)
+    lv = _random_levels(rng, 8, h, w)
+    n = 40
+    pool = sl.game.LevelPool(lv)
+    lazy = sl.env.GlobalCounter()
+    eager = SimpleNamespace(episodes_started=0, episodes_completed=0, num_steps=0)
+    a = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=lazy, compute_obs=(h == 26), auto_reset=auto, time_limit=9)
+    b = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=eager, compute_obs=False, auto_reset=auto, time_limit=9)
+    for e in (a, b):
+        e.seed(3)
+        e.reset()
+    for t in range(30):
+        acts = rng.randint(9, size=n)
+        _, ra, da, _ = a.step(acts)
+        _, rb, db, _ = b.step(acts)
+        assert (ra == rb).all() and (da == db).all()
+        if t % 7 == 6:
+            assert lazy.num_steps == eager.num_steps and lazy.episodes_completed == eager.episodes_completed, t
+    assert lazy.episodes_started == eager.episodes_started == n
+    assert lazy.num_steps == eager.num_steps > 0 and lazy.episodes_completed == eager.episodes_completed > 0
+    before = eager.num_steps
+    lazy.num_steps = 5  # assignable, and keeps counting from there
+    a.step(acts)
+    b.step(acts)
+    assert lazy.num_steps == 5 + (eager.num_steps - before)
+    # the class-level default is a GlobalCounter shared by envs that are not given their own
+    assert isinstance(sl.env.SafeLifeEnv.global_counter, sl.env.GlobalCounter)
+
+
+def test_step_returns_fresh_tensors(sl):
+    lv = gu.level_slice(gu.levels("prune-spawn"), 0, 8)
+    env = sl.env.SafeLifeEnv(sl.game.LevelPool(lv), num_envs=16, global_counter=None)
+    env.seed(0)
+    env.reset()
+    rs, ds = [], []
+    rng = np.random.RandomState(0)
+    for _ in range(6):
+        _, r, d, _ = env.step(rng.randint(5, 9, size=16))
+        rs.append(r)
+        ds.append(d)
+    assert len({r.data_ptr() for r in rs}) == 6 and len({d.data_ptr() for d in ds}) == 6
+    assert any(int(r.abs().sum()) for r in rs) and rs[0].dtype == torch.int32
+
+
+def test_speedups_batch_streams_continue(sl):
+    """speedups.advance_board on a batch: board i keeps consuming env i's stream over successive calls (the
+    reference's stream keeps running too); seed() rewinds.  numpy and tensor batches, vs the oracle."""
+    sp = sl.speedups
+    lv = gu.levels("prune-spawn")
+    b0 = lv["board"][:12].copy()
+    n, h, w = b0.shape
+    for tensor in (False, True):
+        sp.seed(41)
+        ctr = np.zeros(n, dtype=np.uint64)
+        cur = torch.from_numpy(b0).cuda() if tensor else b0
+        ocur = b0.copy()
+        firsts = []
+        for k in range(4):
+            cur = sp.advance_board(cur, 0.3)
+            nxt = np.empty_like(ocur)
+            for i in range(n):
+                nxt[i], c = slo.advance_board(ocur[i], 0.3, seed=41, env=i, counter=int(ctr[i]))
+                ctr[i] = c
+            ocur = nxt
+            got = cur.cpu().numpy() if tensor else cur
+            assert (got == ocur).all(), (tensor, k)
+            firsts.append(got.copy())
+        assert ctr.min() > 0
+        sp.seed(41)  # rewinds every board's stream
+        again = sp.advance_board(torch.from_numpy(b0).cuda() if tensor else b0, 0.3)
+        again = again.cpu().numpy() if tensor else again
+        assert (again == firsts[0]).all()
+
+
+@pytest.mark.parametrize("n,h,w,k", [(1, 26, 26, 1), (3, 26, 26, 3), (20, 26, 26, 1), (700, 26, 26, 2),
+                                     (2, 9, 40, 1), (3, 9, 40, 3), (300, 40, 33, 2)])
+def test_advance_board_host_paths(sl, n, h, w, k):
+    """slb_advance_board_host (what speedups.advance_board(ndarray) binds): the zero-copy path (a few boards read
+    from / written to the pinned block by the kernel itself), the pinned staging path and shapes that need the
+    scratch board, with draw counters in and out, vs the oracle; repeated calls reuse the cached blocks."""
+    rng = np.random.RandomState(n + h)
+    vals = np.array([0, 0, 1033, 521, 16, 1041, 32788, 1688, 152, 9], np.uint16)
+    L = sl.lib.load()
+    for rep in range(3):
+        b = vals[rng.randint(len(vals), size=(n, h, w))]
+        p = rng.choice([0.0, 0.3, 1.0], size=n).astype(np.float32)
+        ctr = rng.randint(0, 1000, size=n).astype(np.uint64)
+        out = np.empty_like(b)
+        c2 = ctr.copy()
+        sl.lib.check(L.slb_advance_board_host(b.ctypes.data, out.ctypes.data, n, h, w, p.ctypes.data, 9, 100,
+                                              c2.ctypes.data, k))
+        for i in range(n):
+            x, c = b[i], int(ctr[i])
+            for _ in range(k):
+                x, c = slo.advance_board(x, float(p[i]), seed=9, env=100 + i, counter=c)
+            assert (out[i] == x).all(), (rep, i)
+            assert int(c2[i]) == c, (rep, i)
+    # NULL counters: streams start at draw 0
+    out = np.empty_like(b)
+    sl.lib.check(L.slb_advance_board_host(b.ctypes.data, out.ctypes.data, n, h, w, p.ctypes.data, 9, 0, None, 1))
+    for i in range(min(n, 8)):
+        assert (out[i] == slo.advance_board(b[i], float(p[i]), seed=9, env=i, counter=0)[0]).all()
+
+
+def test_host_step_slot_regrows_with_a_step_in_flight(sl):
+    """Two batches of different sizes sharing one stream through the async host step: the second needs a larger
+    staging block while the first step's outputs are still pending (they must be delivered first)."""
+    lv = gu.level_slice(gu.levels("append-spawn"), 0, 10)
+    pool = sl.game.LevelPool(lv)
+    st = torch.cuda.Stream()
+    envs, refs = [], []
+    for n in (64, 1500):
+        for lst in (envs, refs):
+            e = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False)
+            e.seed(2)
+            e.reset()
+            lst.append(e)
+    rng = np.random.RandomState(0)
+    a0 = rng.randint(9, size=64).astype(np.uint8)
+    a1 = rng.randint(9, size=1500).astype(np.uint8)
+    r0, d0 = np.zeros(64, np.int32), np.zeros(64, np.uint8)
+    r1, d1 = np.zeros(1500, np.int32), np.zeros(1500, np.uint8)
+    envs[0].step_host(a0, r0, d0, sync=False, stream=st)      # not waited for
+    envs[1].step_host(a1, r1, d1, sync=True, stream=st)       # larger block on the same slot
+    _, rr0, dd0, _ = refs[0].step(a0)
+    _, rr1, dd1, _ = refs[1].step(a1)
+    assert (r0 == rr0.cpu().numpy()).all() and (d0 == dd0.cpu().numpy()).all()
+    assert (r1 == rr1.cpu().numpy()).all() and (d1 == dd1.cpu().numpy()).all()
+
+
+# ---------------------------------------------------------------------------------------------
+# parity hardening
+# ---------------------------------------------------------------------------------------------
+def _run_vs_oracle(sl, lv, n, steps, seed, auto_reset, time_limit, env0=11, every=20, threads=8):
+    pool = sl.game.LevelPool(lv)
+    P = pool.n_levels
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=env0, global_counter=None, compute_obs=False,
+                             auto_reset=auto_reset, time_limit=time_limit)
+    env.seed(seed)
+    env.reset()
+    lvl = (np.arange(n) + env0) % P
+    o = slo.OracleBatchEnv(slo.OraclePool(**lv), lvl, seed=seed, env_id0=env0, threads=threads, time_limit=time_limit)
+    rng = np.random.RandomState(seed + 1000)
+    stride = n % P or P
+    for t in range(steps):
+        acts = rng.randint(9, size=n)
+        _, r, d, _ = env.step(acts)
+        orr, od = o.step(acts)
+        assert (r.cpu().numpy() == orr).all() and (d.cpu().numpy() == (od != 0)).all(), t
+        if auto_reset and od.any():
+            idx = np.nonzero(od)[0]
+            lvl[idx] = (lvl[idx] + stride) % P
+            o.reset(idx, lvl[idx])
+        if t % every == 0 or t == steps - 1:
+            st, ost = env.game.state_numpy(), o.states
+            assert (env.game.board.cpu().numpy() == o.boards).all(), t
+            assert (env.game.goals.cpu().numpy() == o.goals).all(), t
+            for f in st.dtype.names:
+                assert (st[f] == ost[f]).all(), (f, t)
+    return env, o
+
+
+def test_big_board_fused_step_at_length(sl):
+    """The 256x256 fused step (big_env_kernel: actions + physics + reward + exit paint) on dense random levels —
+    crates, spawners, exits and life everywhere, so that pushes / pulls cross the 32-bit word seams and the torus
+    edge, spawners draw every step and agents exit (auto-reset) — 24 envs x 128 steps, every env against the
+    oracle: rewards and dones every step, full boards / goals / state every 16 steps."""
+    rng = np.random.RandomState(256)
+    lv = _random_levels(rng, 6, 256, 256, exits=40)
+    # agents start on word seams / the torus edge in some levels
+    for l, (x, y) in enumerate([(31, 5), (32, 255), (0, 0), (255, 128), (63, 64), (224, 31)]):
+        ax, ay = lv["agent_loc"][l]
+        lv["board"][l, ay, ax] = 0
+        lv["board"][l, y, x] = 122 | (int(rng.randint(8)) << 9)
+        lv["agent_loc"][l] = (x, y)
+    _run_vs_oracle(sl, lv, 24, 128, seed=5, auto_reset=True, time_limit=50, every=16)
+
+
+@pytest.mark.parametrize("archive", gu.ARCHIVES)
+def test_soak_every_archive(sl, archive):
+    """Bounded soak: 64 envs x 300 steps of every v1.0 archive with and without auto-reset against the oracle,
+    then the side-effect count maps of 8 of those episodes against the oracle's."""
+    lv = gu.levels(archive)
+    _run_vs_oracle(sl, lv, 64, 300, seed=1, auto_reset=True, time_limit=37, every=50)
+    env, o = _run_vs_oracle(sl, lv, 64, 300, seed=2, auto_reset=False, time_limit=1000, every=50)
+    g = env.game
+    st = g.state_numpy()
+    b0 = lv["board"][st["level_id"]]
+    b1 = g.board.cpu().numpy()
+    ctr0 = st["rng_counter"].astype(np.int64)
+    ctr = torch.from_numpy(ctr0.copy()).cuda()
+    spawn = lv["spawn_prob"][st["level_id"]].astype(np.float32)
+    keys, counts, nkeys = sl.se.side_effect_counts(torch.from_numpy(b0).cuda(), g.board, st["num_steps"].astype(np.int32),
+                                                   spawn, num_samples=1000, seed=2, env_id0=11, counters=ctr, kmax=32)
+    keys, counts, nk, ctr = keys.cpu().numpy(), counts.cpu().numpy(), nkeys.cpu().numpy(), ctr.cpu().numpy()
+    for i in range(0, 64, 8):
+        ok, oc, octr = slo.side_effect_counts(b0[i], b1[i], int(st["num_steps"][i]), num_samples=1000,
+                                              spawn_prob=float(spawn[i]), seed=2, env=11 + i, counter=int(ctr0[i]), kmax=32)
+        mine = {int(k): counts[i, :, s] for s, k in enumerate(keys[i]) if k}
+        assert nk[i] == len(ok) and ctr[i] == octr and sorted(mine) == sorted(int(k) for k in ok), i
+        for s, k in enumerate(ok):
+            assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
