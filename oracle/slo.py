@@ -50,9 +50,8 @@ class Pool(C.Structure):
 
 def build(force=False):
     """Compile the oracle port (always) and oracle/_ref (only where /root/reference exists)."""
-    if force or not os.path.exists(_PORT) or (
-        os.path.getmtime(_PORT) < os.path.getmtime(os.path.join(_HERE, "slo_oracle.c"))
-    ):
+    srcs = [os.path.join(_HERE, f) for f in ("slo_oracle.c", "slo_oracle.h", "emd_oracle.c")]
+    if force or not os.path.exists(_PORT) or os.path.getmtime(_PORT) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "port"], stdout=subprocess.DEVNULL)
     if os.path.isdir(os.environ.get("SAFELIFE_REFERENCE", "/root/reference")):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
@@ -99,6 +98,8 @@ def lib():
                                              C.POINTER(C.c_uint64), C.c_int, C.c_void_p,
                                              C.c_void_p]
         L.slo_set_reference_advance.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.slo_emd_transport.restype = C.c_double
+        L.slo_emd_transport.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
