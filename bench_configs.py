@@ -603,6 +603,13 @@ def main():
         out.append(env_step_api_config(reps=300 if quick else 3000))
     if "int_peak" in names:
         out.append(int_peak_config())
+    for nm in names:  # step:<archive|mixed>:<envs> — the fused step on any batch size
+        if nm.startswith("step:"):
+            _, arch, cnt = nm.split(":")
+            lv = mixed_levels() if arch == "mixed" else gu.levels(arch)
+            out.append(step_config("step_%s_%s" % (arch, cnt), lv, int(cnt), 26, 26, ms, consts=consts))
+        if nm.startswith("big:"):
+            out.append(big_config(int(nm.split(":")[1]), ms))
     if "strong_mixed" in names:
         out.append(strong_config("mixed_26", 65536, 0, 1, torch.device("cuda", 0), ms))
     if "strong_big" in names:

@@ -7,7 +7,7 @@
 
 #include "slb_fast.cuh"
 #include "slb_generic_env.cuh"
-#include "slb_big.cuh"
+#include "slb_big_rows.cuh"
 #include "slb_microbench.cuh"
 
 using namespace slb;
@@ -83,8 +83,26 @@ int allow_smem(K kernel, size_t bytes) {
     return 0;
 }
 
-// launches the big-board env kernel with the stages in a.ops
+// launches the big-board env kernel with the stages in a.ops: the register sliding-window variant where the
+// shape has one (rows of 2 / 4 / 8 words, see slb_big_rows.cuh; SLB_BIG_ROWS=0 turns it off), else the
+// shared-memory snapshot variant
 int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
+    static const bool rows_on = []() { const char *v = getenv("SLB_BIG_ROWS"); return !v || v[0] != '0'; }();
+    if (rows_on && rows_shape(pool->h, pool->w)) {
+        const size_t bytes = rows_smem_bytes(pool->h, pool->w);
+        const int wpr = pool->w / 32;
+        if (wpr == 8) {
+            if (int rc = allow_smem(big_rows_env_kernel<8>, bytes)) return rc;
+            big_rows_env_kernel<8><<<a.n, ROWS_THREADS, bytes, st>>>(*pool, a);
+        } else if (wpr == 4) {
+            if (int rc = allow_smem(big_rows_env_kernel<4>, bytes)) return rc;
+            big_rows_env_kernel<4><<<a.n, ROWS_THREADS, bytes, st>>>(*pool, a);
+        } else {
+            if (int rc = allow_smem(big_rows_env_kernel<2>, bytes)) return rc;
+            big_rows_env_kernel<2><<<a.n, ROWS_THREADS, bytes, st>>>(*pool, a);
+        }
+        return SLB_OK;
+    }
     const size_t bytes = big_smem_bytes(pool->h, pool->w);
     if (int rc = allow_smem(big_env_kernel, bytes)) return rc;
     big_env_kernel<<<a.n, BIG_THREADS, bytes, st>>>(*pool, a);

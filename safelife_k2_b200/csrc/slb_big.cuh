@@ -577,95 +577,7 @@ __device__ inline void big_reset(const slb_pool &pool, int level, const BigGeo &
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(BIG_THREADS, 2)
-big_env_kernel(slb_pool pool, BigArgs a) {
-    extern __shared__ __align__(16) uint32_t big_smem[];
-    __shared__ int scratch[96];
-    __shared__ int warp_tot[BIG_THREADS / 32];
-    __shared__ int sh_act[5];
-    const int i = blockIdx.x;
-    const BigGeo g = big_geo(pool.h, pool.w);
-    BigSmem sm;
-    sm.src = big_smem;
-    sm.elig = big_smem + (size_t)BIG_SRC * g.items;
-    sm.rowf = sm.elig + g.items;
-    sm.warp_tot = warp_tot;
-    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
-    const size_t words = (size_t)16 * g.items;
-    uint32_t *board = a.board + i * words, *goals = a.goals ? a.goals + i * words : nullptr;
-    slb_env_state *st = a.state + i;
-    const int ops = a.ops;
-
-    if (ops & BIG_RESET) {
-        if (a.mask && !a.mask[i]) return;
-        big_reset(pool, a.level_ids[i], g, gb, gg, board, goals, st, scratch);
-        return;
-    }
-    const int level = st->level_id;
-    const uint64_t env = a.env_id0 + (uint64_t)i;
-    int act_reward = 0;
-    if (ops & BIG_ACTION) {
-        if (threadIdx.x < 32) {
-            int ax = st->agent_x, ay = st->agent_y, o = st->orientation, go = st->game_over;
-            const int r = big_action(board, g, gb, pool.w, ax, ay, o, go, a.actions[i], st->can_exit);
-            if (threadIdx.x == 0) { sh_act[0] = ax; sh_act[1] = ay; sh_act[2] = o; sh_act[3] = go; sh_act[4] = r; }
-        }
-        __syncthreads();
-        act_reward = sh_act[4];
-        if (threadIdx.x == 0) {
-            st->agent_x = sh_act[0]; st->agent_y = sh_act[1]; st->orientation = sh_act[2]; st->game_over = sh_act[3];
-            if (!(ops & BIG_BOOK) && a.reward_out) a.reward_out[i] = act_reward;
-        }
-    }
-    uint64_t counter = st->rng_counter;
-    if (ops & BIG_PHYSICS) {
-        const float p = pool.spawn_prob[level];
-        // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
-        counter = big_physics(board, g, gb, sm, p, a.seed, env, counter);
-        __syncthreads();
-        counter = big_physics(goals, g, gg, sm, p, a.seed, env, counter);
-        __syncthreads();
-        if (threadIdx.x == 0) { st->rng_counter = counter; st->num_steps += 1; }
-    }
-    if (!(ops & (BIG_BOOK | BIG_POINTS | BIG_PAINT))) return;
-    const uint32_t *e0 = pool.exit_mask + (size_t)level * g.items;
-    int pts, cur, pos;
-    big_score(board, goals, g, e0, false, scratch, pts, cur, pos);
-    const int baseline = pool.baseline[level];
-    const int completed = cur - baseline, possible = pos - baseline;
-    const int ce = can_exit_rule(st->min_performance, completed, possible);
-    if (ops & BIG_POINTS) {
-        if (threadIdx.x == 0) {
-            if (a.points) a.points[i] = pts;
-            if (a.completed) a.completed[i] = completed;
-            if (a.possible) a.possible[i] = possible;
-            if (a.can_exit) a.can_exit[i] = (uint8_t)ce;
-        }
-        return;
-    }
-    big_paint(board, g, gb, e0, ce);
-    __shared__ int sh_done;
-    if (threadIdx.x == 0) {
-        st->can_exit = ce; st->completed = completed; st->possible = possible;
-        st->flags &= ~SLB_ENV_RESCORE;
-        if (ops & BIG_BOOK) {
-            const int reward = act_reward + pts - st->old_points;
-            const int ep_len = st->episode_length + 1;
-            const int done = (ep_len > a.time_limit) || st->game_over;
-            st->episode_length = ep_len;
-            st->episode_completed = done;
-            st->old_points = pts;
-            st->episode_reward += reward;
-            if (a.reward_out) a.reward_out[i] = reward;
-            if (a.done_out) a.done_out[i] = (uint8_t)done;
-            sh_done = done;
-        }
-    }
-    if (!(ops & BIG_BOOK)) return;
-    __syncthreads();
-    if (a.auto_reset_stride > 0 && sh_done)
-        big_reset(pool, (level + a.auto_reset_stride) % pool.n_levels, g, gb, gg, board, goals, st, scratch);
-}
+// (big_env_kernel itself lives in slb_big_rows.cuh, next to the sliding-window physics it can use)
 
 // SimpleSideEffectPenalty's count of side-effect cells per env (env_wrappers.py:319-346); grid = N
 __global__ void __launch_bounds__(256)

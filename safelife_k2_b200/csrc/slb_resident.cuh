@@ -225,58 +225,67 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
                        uint64_t seed, uint64_t env_id0, int32_t *reward_out, uint8_t *done_out,
                        int auto_reset_stride, int l2_prefetch, unsigned long long *gc) {
     const int lane = threadIdx.x & 31;
-    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    // A warp owns env i, i + W, i + 2 W, ... (W = warps of the grid).  The launcher sizes the grid to one
+    // CTA per RES_WARPS envs up to one resident wave; batches of a few waves get one wave of CTAs whose
+    // warps take several envs in turn, the next env's lines travelling from HBM to L2 while the current one
+    // is computed — two lock-step waves would each pay the whole load / compute / store latency chain.
+    const int stride = gridDim.x * RES_WARPS;
     // Programmatic dependent launch: let the next kernel on the stream begin launching now (its CTAs
     // take the SM slots ours free up); wait for the previous kernel's writes before the first read.
     asm volatile("griddepcontrol.launch_dependents;");
     if (i >= n) return;
     const Geo g = make_geo(HW ? HW : pool.h, HW ? HW : pool.w);
-    const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);  // resident words per board: 16 * H
-    uint32_t *bp = board + off, *gp = goals + off;
-    uint32_t B[16], G[16];
+    const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
     if (l2_prefetch) {
         // While the previous kernel on the stream drains, pull this env's lines from HBM into L2
         // (one 128-byte line per lane).  L2 is the point of coherence, so a line prefetched before
         // the previous kernel's last writes land still reads back current after the wait below.
-        const int nb = (__popc(GB) * 16 * g.h + 127) >> 7, ng = (__popc(GG) * 16 * g.h + 127) >> 7;
-        if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)bp + lane * 128));
-        if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)gp + lane * 128));
+        const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);
+        if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(board + off) + lane * 128));
+        if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(goals + off) + lane * 128));
         if (lane >= 30) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(state + i) + (lane - 30) * 64));
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    EnvRegs e = load_env(state + i);
-    // one-step launches bump the pointers once; the step loop indexes instead (fewer live registers)
-    int action = actions[i];
-    if (ONE) {
-        if (reward_out) reward_out += i;
-        if (done_out) done_out += i;
-    }
-    load_res(bp, g, GB, B);
-    load_res(gp, g, GG, G);
-    LevelConsts lc = load_level(pool, e.level, g);
-    const uint64_t env = env_id0 + (uint64_t)i;
-    bool g_dirty = false;
-    const int steps = ONE ? 1 : t_steps;
+    for (; i < n; i += stride) {
+        const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);  // resident words per board: 16 * H
+        uint32_t *bp = board + off, *gp = goals + off;
+        if (i + stride < n) {  // the next env of this warp: HBM -> L2 while this one is stepped
+            const uint32_t offn = (uint32_t)(i + stride) * (16u * (uint32_t)g.h);
+            if (lane < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(board + offn) + lane * 128));
+            if (lane < ng) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(goals + offn) + lane * 128));
+            if (lane >= 30) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)(state + i + stride) + (lane - 30) * 64));
+        }
+        uint32_t B[16], G[16];
+        EnvRegs e = load_env(state + i);
+        int action = actions[i];
+        load_res(bp, g, GB, B);
+        load_res(gp, g, GG, G);
+        LevelConsts lc = load_level(pool, e.level, g);
+        const uint64_t env = env_id0 + (uint64_t)i;
+        bool g_dirty = false;
+        const int steps = ONE ? 1 : t_steps;
 
-    for (int t = 0; t < steps; t++) {
-        int next_action = 0;
-        if (!ONE && t + 1 < steps) next_action = actions[(size_t)(t + 1) * n + i];
-        int done;
-        const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done, gc, i);
-        if (lane == 0) {
-            const size_t o = ONE ? 0 : (size_t)t * n + i;
-            if (reward_out) reward_out[o] = reward;
-            if (done_out) done_out[o] = (uint8_t)done;
+        for (int t = 0; t < steps; t++) {
+            int next_action = 0;
+            if (!ONE && t + 1 < steps) next_action = actions[(size_t)(t + 1) * n + i];
+            int done;
+            const int reward = env_step_once<GB, GG>(pool, g, B, G, lc, e, action, seed, env, time_limit, g_dirty, done, gc, i);
+            if (lane == 0) {
+                const size_t o = (size_t)t * n + i;
+                if (reward_out) reward_out[o] = reward;
+                if (done_out) done_out[o] = (uint8_t)done;
+            }
+            if (done && auto_reset_stride > 0) {
+                reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
+                g_dirty = true;
+            }
+            action = next_action;
         }
-        if (done && auto_reset_stride > 0) {
-            reset_env_res(pool, (e.level + auto_reset_stride) % pool.n_levels, g, GB, GG, B, G, lc, e);
-            g_dirty = true;
-        }
-        action = next_action;
+        store_res(bp, g, GB, B);
+        if (g_dirty) store_res(gp, g, GG, G);
+        if (lane == 0) store_env(state + i, e);
     }
-    store_res(bp, g, GB, B);
-    if (g_dirty) store_res(gp, g, GG, G);
-    if (lane == 0) store_env(state + i, e);
 }
 
 // picks the smallest instantiated superset of the pool's plane groups
@@ -285,7 +294,21 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
                                    int time_limit, uint64_t seed, uint64_t env0, int32_t *reward,
                                    uint8_t *done, int stride, cudaStream_t st,
                                    unsigned long long *gc = nullptr) {
-    const int grid = (n + RES_WARPS - 1) / RES_WARPS;
+    int grid = (n + RES_WARPS - 1) / RES_WARPS;
+    // more CTAs than one resident wave, up to SLB_RES_ROUNDS waves (default 4): one balanced wave of CTAs
+    // whose warps take `rounds` envs each (see the kernel); larger batches keep one CTA per RES_WARPS envs —
+    // their CTAs are out of step with each other anyway
+    static const int max_rounds = []() { const char *v = getenv("SLB_RES_ROUNDS"); return v ? atoi(v) : 4; }();
+    static const int wave = []() {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        return sms * (SLB_RES_SLOTS / RES_WARPS);
+    }();
+    if (grid > wave && grid <= max_rounds * wave) {
+        const int rounds = (grid + wave - 1) / wave;
+        grid = (grid + rounds - 1) / rounds;
+    }
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     // launched with programmatic stream serialization (see the griddepcontrol pair in the kernel)
     static const bool pdl = []() { const char *v = getenv("SLB_PDL"); return !v || v[0] != '0'; }();
