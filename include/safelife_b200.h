@@ -268,6 +268,30 @@ int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, i
                            uint16_t *d_keys, uint16_t *d_counts, int32_t *d_nkeys,
                            uint16_t *d_scratch, void *stream);
 
+/* ---- "next" row 4: the EMD stage of side_effect_score for a whole batch (side_effects.py:12-56) ---------
+ * The reference hands every (episode, cell type) pair of density maps to third-party pyemd.emd
+ * (pyemd 0.5.1, side_effects.py:56; not available here: the value is "parity unpinned" against pyemd and checked
+ * against two independent CPU solvers).  Here: problem p = i * kmax + slot takes the two uint16 count maps
+ * d_counts[i, 0 / 1, slot] of slb_side_effect_counts (densities = counts / num_samples), the changed cells
+ * (|a - b| > 1e-3 max|a - b|), and computes EMD-hat as pyemd.emd does (Pele & Werman's emd_hat_gd_metric: cancel
+ * min(a, b) inside every cell, exact min-cost transport of the rest, extra_mass_penalty per unit of surplus).
+ * Slots with d_keys[p] == 0 are skipped.
+ * slb_emd_sizes: d_n_src[p] / d_n_snk[p] = number of supplying / demanding cells of problem p (0 for skipped
+ * slots) — what the caller sizes the solver with.
+ * slb_emd_solve: solves the problems d_order[0 .. n_problems) (largest first balances best), one warp each;
+ * d_emd[p] receives the value.  d_lut [H,W] doubles: ground distance of two cells whose coordinates differ by
+ * (|dy|, |dx|) after the wrap (made on the host exactly as side_effects.py:50-55); wrap_x / wrap_y as there.
+ * vmax >= max(n_src + n_snk), ft_stride >= max(n_src * n_snk) over the problems; d_scratch: scratch_doubles
+ * doubles, at least 4 * ft_stride (the grid is sized to what fits); d_queue: one zeroed uint32; d_status: one
+ * zeroed int32, set to 1 if a problem did not converge (its d_emd is -1).  SLB_ERR_UNSUPPORTED when vmax
+ * exceeds the solver's shared memory (about 1800 changed cells). */
+int slb_emd_sizes(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                  int num_samples, int32_t *d_n_src, int32_t *d_n_snk, void *stream);
+int slb_emd_solve(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                  int num_samples, const double *d_lut, int wrap_x, int wrap_y, double extra_mass_penalty,
+                  const int32_t *d_order, int n_problems, int vmax, size_t ft_stride, double *d_scratch,
+                  size_t scratch_doubles, uint32_t *d_queue, double *d_emd, int32_t *d_status, void *stream);
+
 /* ---- statistics vector for the multi-GPU all-reduce -----------------------------
  * d_stats[8] int64 += { sum reward, n done, sum episode_length of done envs, sum episode_reward of
  * done envs, sum completed of done, sum possible of done, n envs stepped, n game_over }. */

@@ -9,6 +9,7 @@
 #include "slb_generic_env.cuh"
 #include "slb_big_rows.cuh"
 #include "slb_microbench.cuh"
+#include "slb_emd.cuh"
 
 using namespace slb;
 
@@ -933,6 +934,63 @@ int slb_side_effect_counts(const uint16_t *d_board0, const uint16_t *d_board1, i
             d_board0, d_board1, h, w, d_num_steps, num_samples, d_spawn_prob, seed, env_id0,
             d_counters, kmax, d_keys, d_counts, d_nkeys, d_scratch);
     }
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+// ---- the EMD stage of side_effect_score, batched (side_effects.py:12-56 -> pyemd.emd) --------------
+static int emd_args(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                    int num_samples, EmdArgs *a) {
+    if (int rc = check_shape(n, h, w)) return rc;
+    if (!d_counts || !d_keys || kmax < 1 || num_samples < 1)
+        return fail(SLB_ERR_INVALID, "slb_emd: bad arguments");
+    if (h > 256 || w > 256) return fail(SLB_ERR_UNSUPPORTED, "slb_emd: boards up to 256 x 256");
+    if ((long long)n * kmax > (1ll << 30)) return fail(SLB_ERR_UNSUPPORTED, "slb_emd: too many problems");
+    *a = EmdArgs{};
+    a->counts = d_counts; a->keys = d_keys; a->n = n; a->kmax = kmax; a->h = h; a->w = w;
+    a->num_samples = (double)num_samples;
+    return SLB_OK;
+}
+
+int slb_emd_sizes(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                  int num_samples, int32_t *d_n_src, int32_t *d_n_snk, void *stream) {
+    EmdArgs a;
+    if (int rc = emd_args(d_counts, d_keys, n, kmax, h, w, num_samples, &a)) return rc;
+    if (!d_n_src || !d_n_snk) return fail(SLB_ERR_INVALID, "slb_emd_sizes: NULL output");
+    if (n == 0) return SLB_OK;
+    const int probs = n * kmax;
+    emd_sizes_kernel<<<(probs + EMD_WARPS - 1) / EMD_WARPS, EMD_WARPS * 32, 0, (cudaStream_t)stream>>>(a, d_n_src, d_n_snk);
+    SLB_LAUNCHED();
+    return SLB_OK;
+}
+
+int slb_emd_solve(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                  int num_samples, const double *d_lut, int wrap_x, int wrap_y, double extra_mass_penalty,
+                  const int32_t *d_order, int n_problems, int vmax, size_t ft_stride, double *d_scratch,
+                  size_t scratch_doubles, uint32_t *d_queue, double *d_emd, int32_t *d_status, void *stream) {
+    EmdArgs a;
+    if (int rc = emd_args(d_counts, d_keys, n, kmax, h, w, num_samples, &a)) return rc;
+    if (!d_lut || !d_order || !d_scratch || !d_queue || !d_emd || !d_status || n_problems < 0 || vmax < 1 ||
+        ft_stride < 1)
+        return fail(SLB_ERR_INVALID, "slb_emd_solve: bad arguments");
+    if (n_problems == 0) return SLB_OK;
+    a.lut = d_lut; a.wrap_x = wrap_x; a.wrap_y = wrap_y; a.extra_mass_penalty = extra_mass_penalty;
+    const size_t smem = emd_smem_per_warp(vmax) * EMD_WARPS;
+    if (smem + kSmemStatic > smem_optin())
+        return fail(SLB_ERR_UNSUPPORTED, "slb_emd_solve: %d changed cells in one density map exceed the solver's "
+                    "shared memory (%zu bytes per CTA)", vmax, smem);
+    if (int rc = allow_smem(emd_solve_kernel, smem)) return rc;
+    int dev = 0, sms = 148, per_sm = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    SLB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emd_solve_kernel, EMD_WARPS * 32, smem));
+    long long grid = (n_problems + EMD_WARPS - 1) / EMD_WARPS;
+    if (grid > (long long)sms * per_sm) grid = (long long)sms * per_sm;
+    const long long by_scratch = (long long)(scratch_doubles / (ft_stride * EMD_WARPS));
+    if (by_scratch < 1) return fail(SLB_ERR_INVALID, "slb_emd_solve: scratch smaller than one CTA's flow matrices");
+    if (grid > by_scratch) grid = by_scratch;
+    emd_solve_kernel<<<(unsigned)grid, EMD_WARPS * 32, smem, (cudaStream_t)stream>>>(
+        a, d_order, n_problems, vmax, d_scratch, ft_stride, d_queue, d_emd, d_status);
     SLB_LAUNCHED();
     return SLB_OK;
 }

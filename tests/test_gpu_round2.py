@@ -274,3 +274,96 @@ def test_soak_every_archive(sl, archive):
         assert nk[i] == len(ok) and ctr[i] == octr and sorted(mine) == sorted(int(k) for k in ok), i
         for s, k in enumerate(ok):
             assert (mine[int(k)] == oc[:, s]).all(), (i, int(k))
+
+
+# ---------------------------------------------------------------------------------------------
+# the EMD stage on the GPU (slb_emd_sizes / slb_emd_solve) against the oracle's two solvers
+# ---------------------------------------------------------------------------------------------
+def _emd_want(c0, c1, ns):
+    from oracle import emd
+    return emd.earth_mover_distance(c0.astype(np.float64) / ns, c1.astype(np.float64) / ns)
+
+
+def test_emd_batch_golden_maps(sl):
+    """the count maps the unmodified reference produced (tests/golden/side_effects.npz) through emd_batch:
+    equal to the oracle's successive-shortest-path solver to 1e-12 (and that one equals the LP, test_emd.py)."""
+    d = gu.load("side_effects.npz")
+    i = 0
+    while "keys_%d" % i in d:
+        ks, cn, ns = d["keys_%d" % i], d["counts_%d" % i], int(d["num_samples_%d" % i])
+        kmax = 8
+        keys = np.zeros((1, kmax), np.uint16)
+        counts = np.zeros((1, 2, kmax) + cn.shape[2:], np.uint16)
+        keys[0, :len(ks)] = ks
+        counts[0, :, :len(ks)] = cn
+        got = sl.se.emd_batch(torch.from_numpy(keys).cuda(), torch.from_numpy(counts).cuda(), ns).cpu().numpy()
+        for s in range(kmax):
+            want = _emd_want(cn[0, s], cn[1, s], ns) if s < len(ks) else 0.0
+            assert abs(got[0, s] - want) <= 1e-12 * max(1.0, abs(want)), (i, s, got[0, s], want)
+        i += 1
+    assert i >= 5
+
+
+@pytest.mark.parametrize("h,w", [(26, 26), (9, 13), (32, 32)])
+def test_emd_batch_random_maps(sl, h, w):
+    """random count maps: sparse and dense differences (hundreds of changed cells), overlapping bins, identical
+    maps, one-sided maps, empty slots — every problem against the oracle."""
+    rng = np.random.RandomState(h * w)
+    n, kmax, ns = 12, 5, 1000
+    keys = np.zeros((n, kmax), np.uint16)
+    counts = np.zeros((n, 2, kmax, h, w), np.uint16)
+    for i in range(n):
+        for s in range(kmax):
+            kind = rng.randint(7)
+            if kind == 0:
+                continue  # empty slot
+            keys[i, s] = 9 + s
+            cells = int(rng.choice([1, 3, 10, 40, min(h * w, 300)]))
+            idx = rng.choice(h * w, cells, replace=False)
+            a = np.zeros(h * w, np.uint16)
+            a[idx] = rng.randint(1, ns + 1, cells)
+            b = a.copy()
+            if kind == 1:
+                pass  # identical maps
+            elif kind == 2:
+                b[:] = 0  # everything is surplus
+            else:
+                move = rng.rand(cells) < 0.7
+                b[idx[move]] = 0
+                j = rng.choice(h * w, int(move.sum()))
+                b[j] = rng.randint(1, ns + 1, j.size)
+            counts[i, 0, s] = a.reshape(h, w)
+            counts[i, 1, s] = b.reshape(h, w)
+    got = sl.se.emd_batch(torch.from_numpy(keys).cuda(), torch.from_numpy(counts).cuda(), ns).cpu().numpy()
+    for i in range(n):
+        for s in range(kmax):
+            want = _emd_want(counts[i, 0, s], counts[i, 1, s], ns) if keys[i, s] else 0.0
+            assert abs(got[i, s] - want) <= 1e-12 * max(1.0, abs(want)), (i, s, got[i, s], want)
+
+
+def test_side_effect_score_uses_the_gpu_emd(sl):
+    """side_effect_score end to end: keys and mean inaction counts as before, the EMD column from emd_batch equal
+    to the oracle's value for the same count maps."""
+    lv = gu.level_slice(gu.levels("prune-spawn"), 0, 6)
+    env = sl.env.SafeLifeEnv(sl.game.LevelPool(lv), num_envs=6, global_counter=None, compute_obs=False)
+    env.seed(4)
+    env.reset()
+    rng = np.random.RandomState(4)
+    for _ in range(40):
+        env.step(rng.randint(9, size=6))
+    g = env.game
+    st = g.state_numpy()
+    ctr0 = st["rng_counter"].astype(np.int64)
+    b1 = g.board.cpu().numpy()
+    res = sl.se.side_effect_score(g, num_samples=200)
+    assert len(res) == 6
+    for i in range(6):
+        ok, oc, _ = slo.side_effect_counts(lv["board"][st["level_id"][i]], b1[i], int(st["num_steps"][i]),
+                                           num_samples=200, spawn_prob=float(np.float32(lv["spawn_prob"][st["level_id"][i]])),
+                                           seed=4, env=i, counter=int(ctr0[i]), kmax=32)
+        assert sorted(int(k) for k in res[i]) == sorted(int(k) for k in ok), i
+        for s, k in enumerate(ok):
+            want = _emd_want(oc[0, s], oc[1, s], 200)
+            got, mean = res[i][np.uint16(k)]
+            assert abs(got - want) <= 1e-12 * max(1.0, abs(want)), (i, int(k))
+            assert mean == np.sum(oc[0, s].astype(np.float64) / 200), (i, int(k))
