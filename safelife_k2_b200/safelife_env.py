@@ -174,6 +174,7 @@ class SafeLifeEnv(object):
     auto_reset = False   # reset finished envs inside the step kernel (ContinuingEnv-like)
     compute_obs = True   # False: step()/reset() return obs=None (policy reads game.board itself)
     level_ids = None     # first level of each env (default: (global env index) % pool size)
+    shard = None         # (lo, hi, total) when made by SafeLifeEnv.sharded
 
     def __init__(self, level_iterator, **kwargs):
         """level_iterator: a LevelPool, or anything LevelPool accepts (structured level array,
@@ -205,7 +206,49 @@ class SafeLifeEnv(object):
             self._next_level = np.asarray(self.level_ids, dtype=np.int64).reshape(self.num_envs) % self.pool.n_levels
         self.seed()
 
+    @classmethod
+    def sharded(cls, level_iterator, total_envs, rank=None, world_size=None, device=None, **kwargs):
+        """This rank's contiguous share of a job of `total_envs` envs (envs shard by global index,
+        one process per GPU, no data-path collective).  rank / world_size default to the torchrun environment
+        (distributed.init_from_env, which also creates the process group for the statistics all-reduce); the
+        level pool is put on this rank's GPU.  An env's levels and spawn stream depend on its GLOBAL index only,
+        so the job's results do not depend on the number of GPUs."""
+        from . import distributed
+        if rank is None or world_size is None:
+            rank, world_size, local = distributed.init_from_env()
+            if device is None:
+                device = torch.device("cuda", local)
+        lo, hi = distributed.shard_range(int(total_envs), int(rank), int(world_size))
+        pool = level_iterator if isinstance(level_iterator, LevelPool) else LevelPool(level_iterator, device=device)
+        base = int(kwargs.pop("env_id0", 0))
+        env = cls(pool, num_envs=hi - lo, env_id0=base + lo, **kwargs)
+        env.shard = (lo, hi, int(total_envs))
+        return env
+
+    def state_dict(self):
+        """Checkpoint of the env batch: the game's state_dict plus the level cursor, the seed and the
+        global counter's values."""
+        gc = self.global_counter
+        return {"game": self.game.state_dict() if self.game is not None else None,
+                "next_level": np.array(self._next_level), "seed": self._seed,
+                "global_counter": None if gc is None else {k: int(getattr(gc, k)) for k in
+                                                           ("episodes_started", "episodes_completed", "num_steps")}}
+
+    def load_state_dict(self, d):
+        if d["game"] is not None:
+            if self.game is None:
+                self.reset()
+            self.game.load_state_dict(d["game"])
+        self._next_level = np.array(d["next_level"])
+        self._seed = int(d["seed"])
+        if d.get("global_counter") is not None and self.global_counter is not None:
+            for k, v in d["global_counter"].items():
+                setattr(self.global_counter, k, v)
+        self._dev_key = None  # rebind the native steppers (the seed may have changed)
+        self._drop_steppers()
+
     # ------------------------------------------------------------------------------------------
+    def seed(self, seed=None):    # ------------------------------------------------------------------------------------------
     def seed(self, seed=None):
         """safelife_env.py:120-123: sets the seed of the spawn streams (the reference reseeds the
         global numpy stream through speedups.seed).  Draw counters restart at the next reset()."""

@@ -438,6 +438,56 @@ class SafeLifeGame(object):
                                                         self.goals_res.data_ptr(), self.state.data_ptr(),
                                                         self._s()))
 
+    # -- checkpoint / resume (GameState.serialize / save / load, safelife_game.py:184-260) -----
+    def serialize(self, i):
+        """GameWithGoals.serialize (safelife_game.py:184-194, 567-574) for env i: a dict in the reference's
+        saved-game format (np.savez_compressed(**d) gives a file its GameState.load reads)."""
+        st = self.state[int(i)].cpu().numpy().view(ENV_STATE_DTYPE)[0]
+        return {
+            "spawn_prob": float(self.pool.host["spawn_prob"][int(st["level_id"])]),
+            "orientation": int(st["orientation"]),
+            "agent_loc": (int(st["agent_x"]), int(st["agent_y"])),
+            "board": self.cells_of(i, "board").cpu().numpy(),
+            "goals": self.cells_of(i, "goals").cpu().numpy(),
+            "class": "safelife.safelife_game.SafeLifeGame",
+            "min_performance": float(st["min_performance"]),
+        }
+
+    def save(self, file_name, i=0):
+        """GameState.save (safelife_game.py:214-227) for env i."""
+        import os
+        file_name = os.path.abspath(os.path.expanduser(file_name))
+        if not file_name.endswith(".npz"):
+            file_name += ".npz"
+        np.savez_compressed(file_name, **self.serialize(i))
+        return file_name
+
+    def state_dict(self):
+        """Everything a batch needs to resume bit-exactly: the resident boards / goals as they are, the env
+        state records (agent, counters, cached score, spawn-stream counters, min_performance), seed and global
+        env index.  CPU tensors; the level pool is not part of it (load into a game on an equal pool)."""
+        return {
+            "format": "safelife_k2_b200.SafeLifeGame/1",
+            "num_envs": self.n, "shape": (self.pool.h, self.pool.w), "n_levels": self.pool.n_levels,
+            "plane_groups": tuple(int(x) for x in self.pool.c.plane_groups),
+            "seed": self.seed, "env_id0": self.env_id0,
+            "board_res": self.board_res.cpu(), "goals_res": self.goals_res.cpu(), "state": self.state.cpu(),
+        }
+
+    def load_state_dict(self, d):
+        if d.get("format") != "safelife_k2_b200.SafeLifeGame/1":
+            raise ValueError("not a SafeLifeGame state_dict")
+        if (d["num_envs"] != self.n or tuple(d["shape"]) != (self.pool.h, self.pool.w)
+                or d["n_levels"] != self.pool.n_levels):
+            raise ValueError("state_dict of a different batch: %d envs of %s on %d levels" % (
+                d["num_envs"], tuple(d["shape"]), d["n_levels"]))
+        if tuple(d["plane_groups"]) != tuple(int(x) for x in self.pool.c.plane_groups):
+            raise ValueError("state_dict was taken on a level pool with other cell types (plane groups differ)")
+        self.seed, self.env_id0 = int(d["seed"]), int(d["env_id0"])
+        self.board_res.copy_(d["board_res"])
+        self.goals_res.copy_(d["goals_res"])
+        self.state.copy_(d["state"])
+
     @property
     def is_stochastic(self):
         return ((self.board.view(torch.int16) & int(CellTypes.spawning)) != 0).flatten(1).any(1)

@@ -367,3 +367,74 @@ def test_side_effect_score_uses_the_gpu_emd(sl):
             got, mean = res[i][np.uint16(k)]
             assert abs(got - want) <= 1e-12 * max(1.0, abs(want)), (i, int(k))
             assert mean == np.sum(oc[0, s].astype(np.float64) / 200), (i, int(k))
+
+
+def test_checkpoint_resume_is_bit_exact(sl, tmp_path):
+    """state_dict / load_state_dict: a batch resumed from a checkpoint continues bit-exactly (boards,
+    goals, state incl. spawn-stream counters, rewards, dones, global counter); serialize / save give the
+    reference's saved-game format."""
+    lv = gu.levels("prune-spawn")
+    pool = sl.game.LevelPool(lv)
+    rng = np.random.RandomState(8)
+    acts = rng.randint(9, size=(60, 200))
+
+    def make():
+        e = sl.env.SafeLifeEnv(pool, num_envs=200, env_id0=7, global_counter=sl.env.GlobalCounter(), compute_obs=False,
+                               auto_reset=True, time_limit=25)
+        e.seed(5)
+        e.reset()
+        return e
+
+    a = make()
+    for t in range(30):
+        a.step(acts[t])
+    ck = a.state_dict()
+    torch.save(ck, str(tmp_path / "ck.pt"))
+    b = make()
+    b.load_state_dict(torch.load(str(tmp_path / "ck.pt"), weights_only=False))
+    for t in range(30, 60):
+        _, ra, da, _ = a.step(acts[t])
+        _, rb, db, _ = b.step(acts[t])
+        assert (ra == rb).all() and (da == db).all(), t
+    assert (a.game.state == b.game.state).all() and (a.game.board_res == b.game.board_res).all()
+    assert (a.game.goals_res == b.game.goals_res).all()
+    assert a.global_counter.num_steps == b.global_counter.num_steps == 60 * 200
+    assert a.global_counter.episodes_completed == b.global_counter.episodes_completed
+    # the reference's saved-game format for one env
+    f = a.game.save(str(tmp_path / "env3"), 3)
+    with np.load(f) as z:
+        assert (z["board"] == a.game.board[3].cpu().numpy()).all() and (z["goals"] == a.game.goals[3].cpu().numpy()).all()
+        st = a.game.state_numpy()[3]
+        assert tuple(z["agent_loc"]) == (st["agent_x"], st["agent_y"]) and int(z["orientation"]) == st["orientation"]
+        assert float(z["min_performance"]) == st["min_performance"]
+
+
+def test_sharded_env_equals_its_slice_of_the_whole_job(sl):
+    """SafeLifeEnv.sharded: rank r of w plays envs shard_range(total, r, w) of the job, with the same results
+    as those envs have in the unsharded batch."""
+    from safelife_k2_b200 import distributed
+    lv = gu.levels("append-spawn")
+    pool = sl.game.LevelPool(lv)
+    total = 300
+    whole = sl.env.SafeLifeEnv(pool, num_envs=total, global_counter=None, compute_obs=False)
+    whole.seed(9)
+    whole.reset()
+    parts = []
+    for r in range(4):
+        e = sl.env.SafeLifeEnv.sharded(pool, total, rank=r, world_size=4, global_counter=None, compute_obs=False)
+        assert e.shard[:2] == distributed.shard_range(total, r, 4)
+        e.seed(9)
+        e.reset()
+        parts.append(e)
+    rng = np.random.RandomState(9)
+    for t in range(25):
+        acts = rng.randint(9, size=total)
+        _, rw, dw, _ = whole.step(acts)
+        for e in parts:
+            lo, hi, _ = e.shard
+            _, r, d, _ = e.step(acts[lo:hi])
+            assert (r == rw[lo:hi]).all() and (d == dw[lo:hi]).all(), (t, lo)
+    for e in parts:
+        lo, hi, _ = e.shard
+        assert (e.game.state == whole.game.state[lo:hi]).all()
+        assert (e.game.board == whole.game.board[lo:hi]).all()
