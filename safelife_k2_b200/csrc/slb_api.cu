@@ -330,8 +330,10 @@ int slb_advance_board_host(const uint16_t *h_in, uint16_t *h_out, int n, int h, 
         memcpy(a->h + o_p, h_spawn_prob, (size_t)n * 4);
         if (h_counters) memcpy(a->h + o_c, h_counters, (size_t)n * 8);
         else memset(a->h + o_c, 0, (size_t)n * 8);
+        t_advance_no_bulk = true;
         rc = slb_advance_board((const uint16_t *)a->h, (uint16_t *)(a->h + o_out), n, h, w, (const float *)(a->h + o_p),
                                seed, env_id0, (uint64_t *)(a->h + o_c), k_steps, nullptr, st);
+        t_advance_no_bulk = false;
         if (rc != SLB_OK) return rc;
         SLB_CUDA(cudaStreamSynchronize(st));
         memcpy(h_out, a->h + o_out, cells * 2);

@@ -114,6 +114,38 @@ __host__ __device__ __forceinline__ int row_stride(int w) {
     return s;
 }
 
+// the planes of the board whose cells lie in shared memory at `sm` (row stride row_stride(w)); lane = row
+template <int HW = 0>
+__device__ __forceinline__ void planes_from_image(const uint16_t *sm, int h_, int w_, uint32_t P[16]) {
+    const int h = HW ? HW : h_, w = HW ? HW : w_;
+    const int lane = threadIdx.x & 31, S = row_stride(w);
+    uint32_t x[16];
+    const uint32_t *row = reinterpret_cast<const uint32_t *>(sm) + lane * (S >> 1);
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        uint32_t v = 0;
+        if (lane < h && 2 * j < w) {
+            v = row[j];
+            if (2 * j + 1 >= w) v &= 0xffffu;
+        }
+        x[j] = v;
+    }
+    cells_to_planes(x, P);
+}
+
+// the inverse: the planes written as cells into the shared image (callers sync the warp around it)
+template <int HW = 0>
+__device__ __forceinline__ void image_from_planes(uint16_t *sm, int h_, int w_, const uint32_t P[16]) {
+    const int h = HW ? HW : h_, w = HW ? HW : w_;
+    const int lane = threadIdx.x & 31, S = row_stride(w);
+    uint32_t x[16];
+    planes_to_cells(P, x);
+    uint32_t *row = reinterpret_cast<uint32_t *>(sm) + lane * (S >> 1);
+#pragma unroll
+    for (int j = 0; j < 16; j++)
+        if (lane < h && 2 * j < w) row[j] = x[j];  // a padding half-word may be written: never read back
+}
+
 // vec: all boards are 8-byte aligned and S == w (then the smem image equals the memory image)
 // HW > 0: the board is HW x HW, known at compile time (row predicates and strides fold away).
 template <int HW = 0>
@@ -133,18 +165,7 @@ __device__ __forceinline__ void load_planes(const uint16_t *__restrict__ src, ui
         }
     }
     __syncwarp();
-    uint32_t x[16];
-    const uint32_t *row = reinterpret_cast<const uint32_t *>(sm) + lane * (S >> 1);
-#pragma unroll
-    for (int j = 0; j < 16; j++) {
-        uint32_t v = 0;
-        if (lane < h && 2 * j < w) {
-            v = row[j];
-            if (2 * j + 1 >= w) v &= 0xffffu;
-        }
-        x[j] = v;
-    }
-    cells_to_planes(x, P);
+    planes_from_image<HW>(sm, h, w, P);
 }
 
 template <int HW = 0>
