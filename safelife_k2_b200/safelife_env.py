@@ -248,7 +248,6 @@ class SafeLifeEnv(object):
         self._drop_steppers()
 
     # ------------------------------------------------------------------------------------------
-    def seed(self, seed=None):    # ------------------------------------------------------------------------------------------
     def seed(self, seed=None):
         """safelife_env.py:120-123: sets the seed of the spawn streams (the reference reseeds the
         global numpy stream through speedups.seed).  Draw counters restart at the next reset()."""

@@ -113,3 +113,15 @@ def test_fast_binding_of_the_host_step_calls():
     assert b"stepper is NULL" in L.slb_last_error()
     assert _slbfast.wait(0) == _lib.SLB_ERR_INVALID
     assert _slbfast.step(None, None, None, None) == _lib.SLB_ERR_INVALID
+
+
+def test_every_product_module_imports_without_a_gpu():
+    """host-side modules must at least import (and the benches compile) on a box without a GPU"""
+    import importlib
+    import py_compile
+
+    for m in ("_lib", "safelife_game", "safelife_env", "env_wrappers", "side_effects", "speedups", "benchmarking",
+              "distributed"):
+        importlib.import_module("safelife_k2_b200." + m)
+    for f in ("bench.py", "bench_configs.py", "__graft_entry__.py", "scripts/sanitize_paths.py"):
+        py_compile.compile(os.path.join(ROOT, f), doraise=True)
