@@ -89,7 +89,8 @@ def time_graph(graph, min_ms=50.0, dev=None, world=1, tail=None, max_reps=200000
     graph.replay()
     e1.record()
     torch.cuda.synchronize()
-    reps = int(min(max_reps, max(1, math.ceil(min_ms / max(e0.elapsed_time(e1), 1e-4)))))
+    # (+ 15 %: the calibration replay runs a little slower than the steady state)
+    reps = int(min(max_reps, max(1, math.ceil(1.15 * min_ms / max(e0.elapsed_time(e1), 1e-4)))))
     if world > 1:
         reps = int(distributed.max_over_ranks(float(reps), dev))
         torch.distributed.barrier()

@@ -217,10 +217,13 @@ inline void launch_advance_fast(const uint16_t *in, uint16_t *out, int n, int h,
                                 uint64_t seed, uint64_t env0, uint64_t *ctr, int k, cudaStream_t st) {
     if (h == 26 && w == 26) {
         // pairs of boards through bulk async copies (both arrays 16-byte aligned; SLB_ADVANCE_BULK=0: off);
-        // an odd last board takes the one-board-per-warp kernel
+        // an odd last board takes the one-board-per-warp kernel.  Only for ONE step per call, the HBM-bound
+        // case: measured on B200 (round 2) still boards 0.122 -> 0.068 ms per 131 072 boards (0.44 -> 0.79 of
+        // HBM), spawner boards 0.182 -> 0.168 ms; with k = 32 steps on chip the call is bound by the integer
+        // pipe and the persistent warps' static share of boards costs 15-22 % against one board per warp
         static const bool bulk = []() { const char *v = getenv("SLB_ADVANCE_BULK"); return !v || v[0] != '0'; }();
         int done = 0;
-        if (bulk && !t_advance_no_bulk && n >= 2 && ((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0) {
+        if (bulk && k == 1 && !t_advance_no_bulk && n >= 2 && ((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0) {
             static const int max_ctas = []() {
                 int dev = 0, sms = 148, per = 1;
                 cudaGetDevice(&dev);

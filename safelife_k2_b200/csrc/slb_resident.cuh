@@ -226,10 +226,10 @@ res_env_rollout_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, s
                        int auto_reset_stride, int l2_prefetch, unsigned long long *gc) {
     const int lane = threadIdx.x & 31;
     int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
-    // A warp owns env i, i + W, i + 2 W, ... (W = warps of the grid).  The launcher sizes the grid to one
-    // CTA per RES_WARPS envs up to one resident wave; batches of a few waves get one wave of CTAs whose
-    // warps take several envs in turn, the next env's lines travelling from HBM to L2 while the current one
-    // is computed — two lock-step waves would each pay the whole load / compute / store latency chain.
+    // A warp owns env i, i + W, i + 2 W, ... (W = warps of the grid).  By default the grid is one CTA per
+    // RES_WARPS envs (the loop runs once); with SLB_RES_ROUNDS > 1 the launcher may give a warp several envs,
+    // the next env's lines travelling from HBM to L2 while the current one is computed (see the launcher for
+    // what that measured).
     const int stride = gridDim.x * RES_WARPS;
     // Programmatic dependent launch: let the next kernel on the stream begin launching now (its CTAs
     // take the SM slots ours free up); wait for the previous kernel's writes before the first read.
@@ -295,10 +295,12 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
                                    uint8_t *done, int stride, cudaStream_t st,
                                    unsigned long long *gc = nullptr) {
     int grid = (n + RES_WARPS - 1) / RES_WARPS;
-    // more CTAs than one resident wave, up to SLB_RES_ROUNDS waves (default 4): one balanced wave of CTAs
-    // whose warps take `rounds` envs each (see the kernel); larger batches keep one CTA per RES_WARPS envs —
-    // their CTAs are out of step with each other anyway
-    static const int max_rounds = []() { const char *v = getenv("SLB_RES_ROUNDS"); return v ? atoi(v) : 4; }();
+    // SLB_RES_ROUNDS = R > 1 (default 1 = off): a batch of up to R resident waves is launched as ONE balanced
+    // wave of CTAs whose warps take several envs in turn (see the kernel).  Measured on B200 (round 2,
+    // profiles/r02): +7 % on append-still at 8 192 envs (uniform cost per env), but -10 % on the mixed archives
+    // at 8 192 / 16 384 envs and on prune-spawn at 16 384 — a static share per warp loses the hardware CTA
+    // scheduler's dynamic balancing when the cost per env varies (spawners, oscillators) — hence off.
+    static const int max_rounds = []() { const char *v = getenv("SLB_RES_ROUNDS"); return v ? atoi(v) : 1; }();
     static const int wave = []() {
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
