@@ -8,6 +8,12 @@ P="python scripts/profile_kernels.py"
 NF="ncu --set full --clock-control none --import-source on"
 python -m pytest tests/test_zz_no_alloc.py -m gpu -q > $O/z_alone.log 2>&1; tail -3 $O/z_alone.log
 python -m pytest tests -x -q -m gpu > $O/z_all.log 2>&1; tail -4 $O/z_all.log
+# A/B: batches of several waves cut into wave-sized launches (SLB_RES_CHUNK), no profiler
+(python bench_configs.py step:mixed:4096 step:mixed:8192 step:mixed:16384 step:prune-spawn:16384 step:mixed:65536;
+ SLB_RES_CHUNK=4096 python bench_configs.py step:mixed:8192 step:mixed:16384 step:prune-spawn:16384 step:mixed:65536 step:append-still:8192;
+ SLB_RES_CHUNK=-1 python bench_configs.py step:mixed:8192 step:mixed:16384 step:prune-spawn:16384;
+ SLB_RES_CHUNK=2048 python bench_configs.py step:mixed:8192 step:mixed:16384 step:prune-spawn:16384) > $O/ab2_chunk.jsonl 2>&1
+cut -c1-200 $O/ab2_chunk.jsonl
 $B > $O/p_bench_plain.json 2> $O/p_bench_plain.err &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/r02_launches.csv $B > $O/p_ncu_list.log 2>&1
 $B > /dev/null 2>&1 && $NF -k regex:res_env_rollout -s 40 -c 3 -o $O/r02_step $B > $O/p_ncu_step.log 2>&1
