@@ -340,9 +340,32 @@ inline void launch_res_env_rollout(const slb_pool &pool, int n, uint32_t *board,
         if (pool.h == 26 && pool.w == 26) SLB_ROLL2(GBV, GGV, 26);                                   \
         else SLB_ROLL2(GBV, GGV, 0);                                                                 \
     } while (0)
-    if (!(gg & ~3u) && !(gb & ~7u)) SLB_ROLL(7u, 3u);        // no spawners anywhere, plain goals
-    else if (!(gg & ~3u)) SLB_ROLL(15u, 3u);                 // spawners on the boards, plain goals
-    else SLB_ROLL(15u, 15u);
+    // SLB_RES_CHUNK = C > 0 (one-step launches only): a batch of more than C envs goes out as ceil(n / C)
+    // launches of at most C envs each (C = -1: one resident wave), back to back on the stream with
+    // programmatic serialization — every launch is then the one-wave case whose loads the previous launch's
+    // tail hides (L2 prefetch ahead of the dependency wait), instead of two or three lock-step waves that
+    // each pay the whole load -> compute -> store latency chain.  An env's results do not depend on how the
+    // batch is cut (its stream is keyed by env0 + index).
+    static const int chunk_cfg = []() { const char *v = getenv("SLB_RES_CHUNK"); return v ? atoi(v) : 0; }();
+    const int chunk = (t_steps == 1 && chunk_cfg != 0) ? (chunk_cfg < 0 ? wave * RES_WARPS : chunk_cfg) : 0;
+    const int n_all = n;
+    uint32_t *const board0 = board, *const goals0 = goals;
+    slb_env_state *const state0 = state;
+    const uint8_t *const actions0 = actions;
+    int32_t *const reward0 = reward;
+    uint8_t *const done0 = done;
+    const uint64_t env00 = env0;
+    for (int lo = 0; lo < n_all; lo += (chunk > 0 ? chunk : n_all)) {
+        n = (chunk > 0 && n_all - lo > chunk) ? chunk : n_all - lo;
+        const size_t woff = (size_t)lo * 16u * (size_t)pool.h;
+        board = board0 + woff; goals = goals0 + woff; state = state0 + lo; actions = actions0 + lo;
+        reward = reward0 ? reward0 + lo : nullptr; done = done0 ? done0 + lo : nullptr;
+        env0 = env00 + (uint64_t)lo;
+        if (chunk > 0) cfg.gridDim = dim3((n + RES_WARPS - 1) / RES_WARPS);
+        if (!(gg & ~3u) && !(gb & ~7u)) SLB_ROLL(7u, 3u);        // no spawners anywhere, plain goals
+        else if (!(gg & ~3u)) SLB_ROLL(15u, 3u);                 // spawners on the boards, plain goals
+        else SLB_ROLL(15u, 15u);
+    }
 #undef SLB_ROLL3
 #undef SLB_ROLL2
 #undef SLB_ROLL
