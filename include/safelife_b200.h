@@ -292,6 +292,22 @@ int slb_emd_solve(const uint16_t *d_counts, const uint16_t *d_keys, int n, int k
                   const int32_t *d_order, int n_problems, int vmax, size_t ft_stride, double *d_scratch,
                   size_t scratch_doubles, uint32_t *d_queue, double *d_emd, int32_t *d_status, void *stream);
 
+/* slb_emd_solve for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as slb_emd_solve, without d_scratch / scratch_doubles / d_queue: the
+ * flow matrices and the queue word live in a static device array of SLB_EMD_STATIC_SCRATCH_DOUBLES doubles
+ * (16 MiB) that every GPU which loads the library holds until exit.  The call allocates and frees nothing (no
+ * cudaMalloc / cudaFree, no allocating library routine); it clears the queue word on `stream` itself.
+ * Limit: ft_stride * 4 <= SLB_EMD_STATIC_SCRATCH_DOUBLES, i.e. n_src * n_snk <= 524 288 per problem (every
+ * 26 x 26 density map fits: <= 338 * 338); beyond that SLB_ERR_UNSUPPORTED with a message naming the limit —
+ * use slb_emd_solve.  All calls on a device share the array: two calls that overlap on the GPU (different
+ * streams, or different host threads / processes' streams of one context) race; calls on one stream are safe. */
+#define SLB_EMD_STATIC_SCRATCH_DOUBLES 2097152
+int slb_emd_solve_static(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                         int num_samples, const double *d_lut, int wrap_x, int wrap_y,
+                         double extra_mass_penalty, const int32_t *d_order, int n_problems, int vmax,
+                         size_t ft_stride, double *d_emd, int32_t *d_status, void *stream);
+
 /* ---- statistics vector for the multi-GPU all-reduce -----------------------------
  * d_stats[8] int64 += { sum reward, n done, sum episode_length of done envs, sum episode_reward of
  * done envs, sum completed of done, sum possible of done, n envs stepped, n game_over }. */

@@ -71,6 +71,8 @@ SYMBOLS = {
     "slb_emd_sizes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "slb_emd_solve": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _i, C.c_double, _vp, _i, _i, _sz, _vp, _sz,
                            _vp, _vp, _vp, _vp]),
+    "slb_emd_solve_static": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _i, C.c_double, _vp, _i, _i, _sz,
+                                  _vp, _vp, _vp]),
     "slb_get_obs": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "slb_env_step_obs": (_i, [_PP, _i, _vp, _vp, _vp, _vp, _i, _u64, _u64, _vp, _vp, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
     "slb_get_obs_channels": (_i, [_PP, _i, _vp, _vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),

@@ -997,6 +997,51 @@ int slb_emd_solve(const uint16_t *d_counts, const uint16_t *d_keys, int n, int k
     return SLB_OK;
 }
 
+// ---- slb_emd_solve for callers that cannot allocate (no counterpart in the reference) ----------------------
+// The solver's scratch — the work-queue word, then the flow matrices — in a file-scope device array that every
+// GPU which loads the library holds until exit.  In host code `g_emd_static` is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr size_t kEmdStaticDoubles = (size_t)SLB_EMD_STATIC_SCRATCH_DOUBLES;
+constexpr size_t kEmdStaticHead = 32;  // doubles in front of the flow matrices; the queue word is the first
+static __device__ __align__(256) double g_emd_static[kEmdStaticHead + kEmdStaticDoubles];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::atomic<double *> g_emd_static_ptr[kMaxDevices];
+
+int emd_static_address(double **out) {
+    int dev = 0;
+    SLB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(SLB_ERR_UNSUPPORTED, "slb_emd_solve_static: device %d", dev);
+    double *p = g_emd_static_ptr[dev].load(std::memory_order_acquire);
+    if (!p) {  // (two threads racing here both get the same answer)
+        SLB_CUDA(cudaGetSymbolAddress((void **)&p, g_emd_static));
+        if (!p) return fail(SLB_ERR_CUDA, "slb_emd_solve_static: cudaGetSymbolAddress returned NULL");
+        g_emd_static_ptr[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return SLB_OK;
+}
+}  // namespace
+
+int slb_emd_solve_static(const uint16_t *d_counts, const uint16_t *d_keys, int n, int kmax, int h, int w,
+                         int num_samples, const double *d_lut, int wrap_x, int wrap_y,
+                         double extra_mass_penalty, const int32_t *d_order, int n_problems, int vmax,
+                         size_t ft_stride, double *d_emd, int32_t *d_status, void *stream) {
+    if (ft_stride < 1 || ft_stride * EMD_WARPS > kEmdStaticDoubles)
+        return fail(SLB_ERR_UNSUPPORTED,
+                    "slb_emd_solve_static: ft_stride = %zu flows per problem exceeds the static scratch "
+                    "(%zu doubles, i.e. ft_stride <= %zu); use slb_emd_solve with a scratch of your own",
+                    ft_stride, kEmdStaticDoubles, kEmdStaticDoubles / EMD_WARPS);
+    double *scratch = nullptr;
+    if (int rc = emd_static_address(&scratch)) return rc;
+    if (n_problems > 0 && d_counts && d_keys)  // the queue must start at zero; the flow matrices are cleared per problem
+        SLB_CUDA(cudaMemsetAsync(scratch, 0, sizeof(uint32_t), (cudaStream_t)stream));
+    return slb_emd_solve(d_counts, d_keys, n, kmax, h, w, num_samples, d_lut, wrap_x, wrap_y, extra_mass_penalty,
+                         d_order, n_problems, vmax, ft_stride, scratch + kEmdStaticHead, kEmdStaticDoubles,
+                         reinterpret_cast<uint32_t *>(scratch), d_emd, d_status, stream);
+}
+
 int slb_microbench_int(int kind, int ctas, int iters, uint32_t *d_sink, uint64_t *h_warp_insts, void *stream) {
     if (ctas < 1 || iters < 1 || !d_sink || (kind != 0 && kind != 1))
         return fail(SLB_ERR_INVALID, "slb_microbench_int: bad arguments");
