@@ -374,6 +374,10 @@ def run_b200(args):
                      "traffic": traffic,
                      "frac_traffic": (traffic / (ms_per_step * 1e-3) / 1e9 / peak) if traffic else None,
                      "traffic_source": consts.get("source"),
+                     # the capture's DRAM bytes + the launch's stores (dirty in L2 when the profiled kernel ends)
+                     "traffic_with_writeback": (traffic + consts.get("store_bytes_per_launch", 0)) if traffic else None,
+                     "frac_traffic_with_writeback": ((traffic + consts.get("store_bytes_per_launch", 0))
+                                                     / (ms_per_step * 1e-3) / 1e9 / peak) if traffic else None,
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": n * BYTES_PER_ENV_STEP,
                      "bytes_per_env_step": BYTES_PER_ENV_STEP,
