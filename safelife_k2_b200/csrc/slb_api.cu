@@ -13,6 +13,10 @@
 
 using namespace slb;
 
+#ifndef SLB_BIG_OPT_DEFAULT
+#define SLB_BIG_OPT_DEFAULT 31
+#endif
+
 namespace {
 
 thread_local char g_err[512] = "";
@@ -92,6 +96,32 @@ int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
     if (rows_on && rows_shape(pool->h, pool->w)) {
         const size_t bytes = rows_smem_bytes(pool->h, pool->w);
         const int wpr = pool->w / 32;
+        // the fused step has its own kernel (slb_big_rows.cuh, rows_step_body); SLB_BIG_OPT picks one of the
+        // compiled variants (0 = the all-stages kernel below), for A/B runs
+        static const int opt = []() { const char *v = getenv("SLB_BIG_OPT"); return v ? atoi(v) : SLB_BIG_OPT_DEFAULT; }();
+        if (a.ops == (BIG_ACTION | BIG_PHYSICS | BIG_BOOK) && opt != 0) {
+#define SLB_ROWS_STEP(WPR_, OPT_)                                                              \
+    do {                                                                                       \
+        if (int rc = allow_smem(big_rows_step_kernel<WPR_, OPT_>, bytes)) return rc;           \
+        big_rows_step_kernel<WPR_, OPT_><<<a.n, ROWS_THREADS, bytes, st>>>(*pool, a);          \
+        return SLB_OK;                                                                         \
+    } while (0)
+            if (wpr == 8) {
+                switch (opt) {
+                case 16: SLB_ROWS_STEP(8, 16);
+                case 17: SLB_ROWS_STEP(8, 17);
+                case 19: SLB_ROWS_STEP(8, 19);
+                case 23: SLB_ROWS_STEP(8, 23);
+                case 29: SLB_ROWS_STEP(8, 29);
+                default: SLB_ROWS_STEP(8, 31);
+                }
+            } else if (wpr == 4) {
+                SLB_ROWS_STEP(4, 31);
+            } else {
+                SLB_ROWS_STEP(2, 31);
+            }
+#undef SLB_ROWS_STEP
+        }
         if (wpr == 8) {
             if (int rc = allow_smem(big_rows_env_kernel<8>, bytes)) return rc;
             big_rows_env_kernel<8><<<a.n, ROWS_THREADS, bytes, st>>>(*pool, a);

@@ -29,13 +29,15 @@ inline bool rows_shape(int h, int w) {
 }
 
 // 6 words per item for the spawn draws + the 11 source planes of every thread's bottom halo row
+// ... + four 16-byte staging slots per thread for the step kernel's asynchronous row copies
 __host__ __device__ inline size_t rows_smem_bytes(int h, int w) {
-    return ((size_t)6 * h * (w / 32) + (size_t)11 * ROWS_THREADS) * 4;
+    return ((size_t)6 * h * (w / 32) + (size_t)12 * ROWS_THREADS + (size_t)16 * ROWS_THREADS) * 4;
 }
 
 struct RowsSmem {
     uint32_t *elig, *rank, *tr, *tg, *tb, *draws;  // [items] each
     uint32_t *halo;                                // [11][ROWS_THREADS]
+    uint32_t *stage;                               // [4][ROWS_THREADS] uint4 (16-byte aligned)
     int *warp_tot;
 };
 
@@ -78,6 +80,32 @@ __device__ __forceinline__ void row_fill(RowRegs &r, const uint4 q[4]) {
     r.s[8] = sp & P[9]; r.s[9] = sp & P[10]; r.s[10] = sp & P[11];
 }
 
+// The same four loads as asynchronous copies into the thread's staging slots (one 16-byte slot per plane group,
+// [group][thread]: conflict-free): no register is tied up while the row travels; row_take_async waits for
+// the thread's own copies and reads the slots.
+template <unsigned GROUPS>
+__device__ __forceinline__ void row_issue_async(const uint32_t *planes, int items, int it, uint4 *stage) {
+    const uint4 *b4 = reinterpret_cast<const uint4 *>(planes);
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(stage);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0), "l"(b4 + it) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0 + 16u * ROWS_THREADS), "l"(b4 + items + it) : "memory");
+    if (GROUPS & 4u)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0 + 32u * ROWS_THREADS), "l"(b4 + 2 * items + it) : "memory");
+    if (GROUPS & 8u)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0 + 48u * ROWS_THREADS), "l"(b4 + 3 * items + it) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+template <unsigned GROUPS>
+__device__ __forceinline__ void row_take_async(const uint4 *stage, uint4 q[4]) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    q[0] = stage[0];
+    q[1] = stage[ROWS_THREADS];
+    q[2] = (GROUPS & 4u) ? stage[2 * ROWS_THREADS] : z;
+    q[3] = (GROUPS & 8u) ? stage[3 * ROWS_THREADS] : z;
+}
+
 // left / right neighbour lanes inside this lane's row segment
 struct RowLanes { int ll, lr; };
 
@@ -109,9 +137,11 @@ __device__ __forceinline__ uint32_t rw_two(const RowRegs &u, const RowRegs &m, c
 // form of SURVEY Appendix A with the lazy-but-exact evaluation of big_rule_items<true>: every lane of the
 // warp calls; summaries that no cell of the warp's rows can need are decided by votes.  Writes the row back
 // if any cell flipped; returns the row's eligible-for-spawning word (parked in shared memory by the caller).
-template <unsigned GROUPS>
+// OUT: col[0..2] receive the row's NEW r / g / b planes (what the fused score of the step kernel reads).
+template <unsigned GROUPS, bool OUT = false>
 __device__ __forceinline__ uint32_t rows_rule(uint32_t *planes, int items, int it, const RowRegs &u, RowRegs &m,
-                                              const RowRegs &d, const RowLanes &L, const RowsSmem &sm) {
+                                              const RowRegs &d, const RowLanes &L, const RowsSmem &sm,
+                                              uint32_t *col = nullptr) {
     const uint32_t a = m.P[0], fz = m.P[4];
     uint32_t is3, is4;
     {
@@ -153,6 +183,9 @@ __device__ __forceinline__ uint32_t rows_rule(uint32_t *planes, int items, int i
         if (any_elig && elig) {  // the colours a spawned cell would take (advance_board.c:110-117)
             sm.tr[it] = tR; sm.tg[it] = tG; sm.tb[it] = tB;
         }
+    }
+    if (OUT) {  // births are flips: without a flip the planes are the old ones
+        col[0] = (m.P[9] & ~flip) | nR; col[1] = (m.P[10] & ~flip) | nG; col[2] = (m.P[11] & ~flip) | nB;
     }
     if (flip) {
         const uint32_t keep = ~flip;
@@ -402,6 +435,323 @@ __global__ void __launch_bounds__(ROWS_THREADS, 2)
 big_rows_env_kernel(slb_pool pool, BigArgs a) {
     extern __shared__ __align__(16) uint32_t big_smem[];
     big_env_body<WPR>(pool, a, big_smem);
+}
+
+
+// =====================================================================================================
+// The fused step (execute_action + advance_board x2 + score + exit colours + bookkeeping) for the sliding-
+// window shapes, restructured around what profiles/r02/b_bigrows_ncu.txt showed: the kernel above issues on
+// 29 % of the cycles with 16 resident warps per SM — it waits on memory — so this variant removes exposed
+// latencies instead of instructions.  OPT bits (compile time; SLB_BIG_OPT picks an instantiation):
+//   RO_PREFETCH  every thread requests its share of the env's board / goals lines into L2 before anything
+//                else happens (state load, action, barriers): the first rows and every later pass hit L2
+//   RO_HOIST     a row's four 16-byte loads are issued at the TOP of the body two rows ahead and land while
+//                the rule of the current row is evaluated (the kernel above issues them at the end of a body
+//                and uses them at once; it only prefetches into L1)
+//   RO_FIXB      the spawn fix-up reads the planes of four items before it modifies and stores any of them
+//                (the loop above is load -> store -> load ...: one L2 round trip per item)
+//   RO_SCORE     when goals hold no spawner, current_points / performance_ratio are accumulated inside the
+//                goals' sliding window (new goal colours are in registers; the board's two plane groups are
+//                requested at the top of the body) instead of a separate pass that reloads both boards
+// Always: slb_env_state lives in shared memory for the whole step (one 80-byte load, one store), the level's
+// exit mask is parked in shared memory while the physics runs, spawn ranks come from ONE CTA-wide scan (a
+// thread owns items / 256 consecutive items) instead of one scan per 256 items.
+// =====================================================================================================
+enum : int { RO_PREFETCH = 1, RO_HOIST = 2, RO_FIXB = 4, RO_SCORE = 8, RO_NEW = 16 };
+
+struct RowsAcc { int pts, cur, pos; };
+
+__device__ __forceinline__ void rows_score_add(RowsAcc &acc, const uint4 &b0, const uint4 &b1, uint32_t g9,
+                                               uint32_t g10, uint32_t g11) {
+    Geo full;
+    full.h = 0; full.w = 32; full.up = full.dn = 0; full.wmask = 0xffffffffu; full.hib = 0x80000000u; full.row = true;
+    uint32_t B[16], G[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) { B[k] = 0u; G[k] = 0u; }
+    B[0] = b0.x; B[4] = b0.y; B[9] = b0.z; B[10] = b0.w;
+    B[11] = b1.x; B[3] = b1.y; B[2] = b1.z; B[15] = b1.w;
+    G[9] = g9; G[10] = g10; G[11] = g11;
+    const RowScore rs = score_planes(B, G, full);
+    acc.pts += rs.points; acc.cur += rs.current; acc.pos += rs.possible;
+}
+
+// One advance_board step of the CTA's board, in place.  SCORE (goals only, GROUPS without spawners): `other`
+// = the env's board, already final; the row's score terms are added to acc.
+template <unsigned GROUPS, int WPR, int OPT, bool SCORE>
+__device__ __forceinline__ uint64_t rows_physics2(uint32_t *planes, int h, const RowsSmem &sm, float spawn_prob,
+                                                  uint64_t seed, uint64_t env, uint64_t counter,
+                                                  const uint32_t *other, RowsAcc &acc) {
+    static_assert(!SCORE || !(GROUPS & 8u), "the fused score needs goals without spawners");
+    constexpr int SUB = 32 / WPR;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int j = lane & (WPR - 1), q = lane / WPR;
+    const int strips = (ROWS_THREADS / 32) * SUB, R = h / strips;
+    const int r0 = (warp * SUB + q) * R;
+    const int items = h * WPR;
+    RowLanes L;
+    L.ll = (lane & ~(WPR - 1)) | ((lane - 1) & (WPR - 1));
+    L.lr = (lane & ~(WPR - 1)) | ((lane + 1) & (WPR - 1));
+    RowRegs A, B, C;
+    uint32_t *halo = sm.halo + threadIdx.x;
+    {
+        uint4 qa[4], qb[4], qc[4], qh[4];
+        row_issue<GROUPS>(planes, items, ((r0 == 0) ? h - 1 : r0 - 1) * WPR + j, qa);
+        row_issue<GROUPS>(planes, items, r0 * WPR + j, qb);
+        row_issue<GROUPS>(planes, items, (r0 + 1) * WPR + j, qc);
+        row_issue<GROUPS>(planes, items, ((r0 + R == h) ? 0 : r0 + R) * WPR + j, qh);
+        if (R > 2) row_prefetch<GROUPS>(planes, items, (r0 + 2) * WPR + j);
+        row_fill(A, qa); row_fill(B, qb); row_fill(C, qc);
+        RowRegs t;
+        row_fill(t, qh);
+#pragma unroll
+        for (int k = 0; k < 11; k++) halo[k * ROWS_THREADS] = t.s[k];
+    }
+    __syncthreads();  // every halo row has been read: stores may begin
+    uint32_t seen = 0;
+    const uint4 *o4 = reinterpret_cast<const uint4 *>(other);
+    uint4 *stage = reinterpret_cast<uint4 *>(sm.stage) + threadIdx.x;  // this thread's slot of each group's block
+#define SLB_ROW_BODY2(UP, MID, DN, K)                                                                    \
+    if ((K) < R) {                                                                                       \
+        const int r_ = r0 + (K);                                                                         \
+        const bool own_ = (K) + 2 < R;                                                                   \
+        const int it_ = r_ * WPR + j;                                                                    \
+        uint4 nq_[4];                                                                                    \
+        if (OPT & RO_HOIST) {                                                                            \
+            if (own_) row_issue_async<GROUPS>(planes, items, (r_ + 2) * WPR + j, stage);                 \
+            if ((K) + 3 < R) row_prefetch<GROUPS>(planes, items, (r_ + 3) * WPR + j);                    \
+        } else if (own_) {                                                                               \
+            row_prefetch<GROUPS>(planes, items, (r_ + 2) * WPR + j);                                     \
+        }                                                                                                \
+        uint4 ob0_, ob1_;                                                                                \
+        if (SCORE) { ob0_ = o4[it_]; ob1_ = o4[items + it_]; }                                           \
+        uint32_t col_[3];                                                                                \
+        const uint32_t e_ = rows_rule<GROUPS, SCORE>(planes, items, it_, UP, MID, DN, L, sm, col_);      \
+        if (GROUPS & 8u) { sm.elig[it_] = e_; seen |= e_; }                                              \
+        if (SCORE) rows_score_add(acc, ob0_, ob1_, col_[0], col_[1], col_[2]);                           \
+        if (own_) {                                                                                      \
+            if (OPT & RO_HOIST) row_take_async<GROUPS>(stage, nq_);                                      \
+            else row_issue<GROUPS>(planes, items, (r_ + 2) * WPR + j, nq_);                              \
+            row_fill(UP, nq_);                                                                           \
+        } else {                                                                                         \
+            _Pragma("unroll") for (int k_ = 0; k_ < 11; k_++) UP.s[k_] = halo[k_ * ROWS_THREADS];        \
+        }                                                                                                \
+    }
+    for (int k = 0; k < R; k += 3) {
+        SLB_ROW_BODY2(A, B, C, k)
+        SLB_ROW_BODY2(B, C, A, k + 1)
+        SLB_ROW_BODY2(C, A, B, k + 2)
+    }
+#undef SLB_ROW_BODY2
+    if (!(GROUPS & 8u)) return counter;
+    if (!__syncthreads_or(seen != 0u)) return counter;  // uniform; also orders the parked words
+    // ---- spawn draws: ONE CTA-wide scan (thread t owns the `per` consecutive items from t * per on, in
+    // raster order), one Philox evaluation per lane packed by votes, fix-up by the same owner ----
+    const int per = items / ROWS_THREADS, i0 = threadIdx.x * per;
+    int cnt = 0;
+    for (int k = 0; k < per; k++) cnt += __popc(sm.elig[i0 + k]);
+    int total;
+    int rank = big_scan(cnt, sm.warp_tot, total);
+    {
+        const uint64_t thr = spawn_threshold(spawn_prob);
+        const int nwarps = ROWS_THREADS >> 5;
+        for (int w0 = warp; w0 * 32 < total; w0 += nwarps) {
+            const int dd = w0 * 32 + lane;
+            const bool hit = dd < total && stream_u53(seed, env, counter + (uint64_t)dd) < thr;
+            const uint32_t word = __ballot_sync(FULL, hit);
+            if (lane == 0) sm.draws[w0] = word;
+        }
+    }
+    __syncthreads();
+    uint4 *b4 = reinterpret_cast<uint4 *>(planes);
+    const int nw = (total + 31) >> 5;
+    constexpr int BATCH = (OPT & RO_FIXB) ? 4 : 1;
+    for (int k0 = 0; k0 < per; k0 += BATCH) {
+        uint32_t sp[BATCH];
+#pragma unroll
+        for (int u = 0; u < BATCH; u++) {
+            sp[u] = 0u;
+            if (k0 + u >= per) continue;
+            uint32_t e = sm.elig[i0 + k0 + u];
+            if (!e) continue;
+            const int w0 = rank >> 5;
+            const uint32_t lo = sm.draws[w0];
+            const uint32_t hi = (w0 + 1 < nw) ? sm.draws[w0 + 1] : 0u;
+            uint32_t bits = __funnelshift_r(lo, hi, (uint32_t)rank & 31u);  // first eligible cell in bit 0
+            rank += __popc(e);
+            uint32_t spawn = 0;
+            while (e) {
+                const uint32_t bit = e & (0u - e);
+                e ^= bit;
+                if (bits & 1u) spawn |= bit;
+                bits >>= 1;
+            }
+            sp[u] = spawn;
+        }
+        uint4 v0[BATCH], v1[BATCH], v2[BATCH], v3[BATCH];
+#pragma unroll
+        for (int u = 0; u < BATCH; u++) {
+            if (!sp[u]) continue;
+            const int it = i0 + k0 + u;
+            v0[u] = b4[it];
+            v1[u] = b4[items + it];
+            if (GROUPS & 4u) v2[u] = b4[2 * items + it];
+            v3[u] = b4[3 * items + it];
+        }
+#pragma unroll
+        for (int u = 0; u < BATCH; u++) {
+            const uint32_t spawn = sp[u];
+            if (!spawn) continue;
+            const int it = i0 + k0 + u;
+            const uint32_t tR = sm.tr[it], tG = sm.tg[it], tB = sm.tb[it];
+            const uint32_t keep = ~spawn;  // spawned cells were dead: their residue bits are discarded
+            uint4 v = v0[u];
+            b4[it] = make_uint4((v.x & keep) | spawn, v.y & keep, (v.z & keep) | (spawn & tR), (v.w & keep) | (spawn & tG));
+            v = v1[u];
+            b4[items + it] = make_uint4((v.x & keep) | (spawn & tB), (v.y & keep) | spawn, v.z & keep, v.w & keep);
+            if (GROUPS & 4u) {
+                v = v2[u];
+                if (v.x | v.y | v.z | v.w) b4[2 * items + it] = make_uint4(v.x & keep, v.y & keep, v.z & keep, v.w & keep);
+            }
+            v = v3[u];
+            if (v.x | v.y | v.z | v.w) b4[3 * items + it] = make_uint4(v.x & keep, v.y & keep, v.z & keep, v.w & keep);
+        }
+    }
+    __syncthreads();
+    return counter + (uint64_t)total;
+}
+
+// the separate score pass (goals with spawners, or RO_SCORE off): two items' loads in flight per thread
+__device__ __forceinline__ void rows_score_pass(const uint32_t *board, const uint32_t *goals, int items, RowsAcc &acc) {
+    const uint4 *b4 = reinterpret_cast<const uint4 *>(board), *g4 = reinterpret_cast<const uint4 *>(goals);
+    for (int it = threadIdx.x; it < items; it += 2 * ROWS_THREADS) {
+        const int i2 = it + ROWS_THREADS;
+        const bool two = i2 < items;
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        const uint4 a0 = b4[it], a1 = b4[items + it], ga0 = g4[it], ga1 = g4[items + it];
+        const uint4 c0 = two ? b4[i2] : z, c1 = two ? b4[items + i2] : z;
+        const uint4 gc0 = two ? g4[i2] : z, gc1 = two ? g4[items + i2] : z;
+        rows_score_add(acc, a0, a1, ga0.z, ga0.w, ga1.x);
+        if (two) rows_score_add(acc, c0, c1, gc0.z, gc0.w, gc1.x);
+    }
+}
+
+template <int WPR, int OPT>
+__device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigArgs &a, uint32_t *big_smem) {
+    __shared__ int scratch[96];
+    __shared__ int warp_tot[32];
+    __shared__ __align__(16) slb_env_state shst;
+    __shared__ int sh_act, sh_baseline, sh_done, sh_reward;
+    __shared__ float sh_prob;
+    const int i = blockIdx.x;
+    const BigGeo g = big_geo(pool.h, pool.w);
+    const int items = g.items;
+    RowsSmem rs;
+    rs.elig = big_smem; rs.rank = rs.elig + items; rs.tr = rs.rank + items; rs.tg = rs.tr + items;
+    rs.tb = rs.tg + items; rs.draws = rs.tb + items; rs.halo = rs.draws + items;
+    rs.stage = rs.halo + 12 * ROWS_THREADS;  // (11 halo planes, padded to keep the slots 16-byte aligned)
+    rs.warp_tot = warp_tot;
+    uint32_t *sh_e0 = rs.rank;  // (the single scan keeps ranks in registers: this array parks the exit mask)
+    const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
+    const size_t words = (size_t)16 * items;
+    uint32_t *board = a.board + i * words, *goals = a.goals + i * words;
+    slb_env_state *st = a.state + i;
+    if (threadIdx.x < 5)
+        reinterpret_cast<uint4 *>(&shst)[threadIdx.x] = reinterpret_cast<const uint4 *>(st)[threadIdx.x];
+    if (threadIdx.x == 32) sh_act = a.actions[i];
+    if (OPT & RO_PREFETCH) {  // 128-byte lines of the groups that exist: items / 8 lines per group
+        const int lpg = items >> 3;
+        for (int k = threadIdx.x; k < 4 * lpg; k += ROWS_THREADS) {
+            const unsigned grp = 1u << (k / lpg);
+            if (gb & grp) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(board) + (size_t)k * 128));
+            if (gg & grp) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(goals) + (size_t)k * 128));
+        }
+    }
+    __syncthreads();
+    const int level = shst.level_id;
+    const uint64_t env = a.env_id0 + (uint64_t)i;
+    const int per = items / ROWS_THREADS, i0 = threadIdx.x * per;
+    {
+        const uint32_t *e0 = pool.exit_mask + (size_t)level * items;
+        for (int k = 0; k < per; k++) sh_e0[i0 + k] = e0[i0 + k];  // read back by the same thread only
+    }
+    if (threadIdx.x == 32) { sh_prob = pool.spawn_prob[level]; sh_baseline = pool.baseline[level]; }
+    if (threadIdx.x < 32) {
+        int ax = shst.agent_x, ay = shst.agent_y, o = shst.orientation, go = shst.game_over;
+        const int r = big_action(board, g, gb, pool.w, ax, ay, o, go, sh_act, shst.can_exit);
+        __syncwarp();
+        if (threadIdx.x == 0) {
+            shst.agent_x = ax; shst.agent_y = ay; shst.orientation = o; shst.game_over = go;
+            sh_reward = r;
+        }
+    }
+    __syncthreads();
+    uint64_t counter = shst.rng_counter;
+    const float p = sh_prob;
+    RowsAcc acc = {0, 0, 0};
+    // board first, then goals: the order the stream is consumed in (safelife_game.py:657-660)
+    if (gb & 8u) counter = rows_physics2<15u, WPR, OPT, false>(board, g.h, rs, p, a.seed, env, counter, nullptr, acc);
+    else if (gb & 4u) counter = rows_physics2<7u, WPR, OPT, false>(board, g.h, rs, p, a.seed, env, counter, nullptr, acc);
+    else counter = rows_physics2<3u, WPR, OPT, false>(board, g.h, rs, p, a.seed, env, counter, nullptr, acc);
+    __syncthreads();
+    bool scored = false;
+    if (gg & 8u) counter = rows_physics2<15u, WPR, OPT, false>(goals, g.h, rs, p, a.seed, env, counter, nullptr, acc);
+    else if (OPT & RO_SCORE) {
+        scored = true;
+        if (gg & 4u) counter = rows_physics2<7u, WPR, OPT, true>(goals, g.h, rs, p, a.seed, env, counter, board, acc);
+        else counter = rows_physics2<3u, WPR, OPT, true>(goals, g.h, rs, p, a.seed, env, counter, board, acc);
+    } else {
+        if (gg & 4u) counter = rows_physics2<7u, WPR, OPT, false>(goals, g.h, rs, p, a.seed, env, counter, nullptr, acc);
+        else counter = rows_physics2<3u, WPR, OPT, false>(goals, g.h, rs, p, a.seed, env, counter, nullptr, acc);
+    }
+    if (!scored) {
+        __syncthreads();
+        rows_score_pass(board, goals, items, acc);
+    }
+    int pts = acc.pts, cur = acc.cur, pos = acc.pos;
+    big_sum3(pts, cur, pos, scratch);  // (its barriers also order the score's reads before the repaint)
+    const int completed = cur - sh_baseline, possible = pos - sh_baseline;
+    const int ce = can_exit_rule(shst.min_performance, completed, possible);
+    // update_exit_colors (safelife_game.py:531-537) from the parked exit mask
+    for (int k = 0; k < per; k++) {
+        const uint32_t m = sh_e0[i0 + k];
+        if (!m) continue;
+        uint32_t P[16];
+        big_load(board, g, i0 + k, gb, P);
+#pragma unroll
+        for (int b = 0; b < 16; b++) P[b] &= ~m;
+        P[4] |= m; P[8] |= m;
+        if (ce) P[9] |= m;
+        big_store(board, g, i0 + k, gb, P);
+    }
+    if (threadIdx.x == 0) {
+        shst.rng_counter = counter; shst.num_steps += 1;
+        shst.can_exit = ce; shst.completed = completed; shst.possible = possible;
+        shst.flags &= ~SLB_ENV_RESCORE;
+        const int reward = sh_reward + pts - shst.old_points;
+        const int ep_len = shst.episode_length + 1;
+        const int done = (ep_len > a.time_limit) || shst.game_over;
+        shst.episode_length = ep_len;
+        shst.episode_completed = done;
+        shst.old_points = pts;
+        shst.episode_reward += reward;
+        if (a.reward_out) a.reward_out[i] = reward;
+        if (a.done_out) a.done_out[i] = (uint8_t)done;
+        sh_done = done;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5)
+        reinterpret_cast<uint4 *>(st)[threadIdx.x] = reinterpret_cast<const uint4 *>(&shst)[threadIdx.x];
+    if (a.auto_reset_stride > 0 && sh_done) {
+        __syncthreads();
+        big_reset(pool, (level + a.auto_reset_stride) % pool.n_levels, g, gb, gg, board, goals, st, scratch);
+    }
+}
+
+template <int WPR, int OPT>
+__global__ void __launch_bounds__(ROWS_THREADS, 2)
+big_rows_step_kernel(slb_pool pool, BigArgs a) {
+    extern __shared__ __align__(16) uint32_t big_smem[];
+    rows_step_body<WPR, OPT>(pool, a, big_smem);
 }
 
 }  // namespace slb

@@ -250,6 +250,22 @@ def test_big_board_fused_step_at_length(sl):
     _run_vs_oracle(sl, lv, 24, 128, seed=5, auto_reset=True, time_limit=50, every=16)
 
 
+@pytest.mark.parametrize("h,w,spawner_goals", [(128, 128, False), (192, 128, True), (256, 64, True),
+                                               (384, 64, False), (256, 256, True)])
+def test_sliding_window_step_every_row_width(sl, h, w, spawner_goals):
+    """The fused step of the sliding-window shapes (rows of 2 / 4 / 8 words; 2 or 3 rows per strip, so that a
+    thread's share of items is not a multiple of the fix-up's batch of four), goals without spawners (score
+    accumulated inside the goals' window) and with spawners (separate score pass), exits + auto-reset: rewards
+    and dones every step, boards / goals / state every 8 steps, against the oracle."""
+    rng = np.random.RandomState(h + w)
+    lv = _random_levels(rng, 4, h, w, exits=12)
+    if spawner_goals:
+        m = rng.rand(*lv["goals"].shape)
+        lv["goals"][m < 0.01] = 1688           # living spawner in the goals
+        lv["goals"][(m >= 0.01) & (m < 0.02)] = 3712  # dead spawner, all colours
+    _run_vs_oracle(sl, lv, 8, 40, seed=7, auto_reset=True, time_limit=17, every=8)
+
+
 @pytest.mark.parametrize("archive", gu.ARCHIVES)
 def test_soak_every_archive(sl, archive):
     """Bounded soak: 64 envs x 300 steps of every v1.0 archive with and without auto-reset against the oracle,
