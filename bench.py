@@ -343,6 +343,9 @@ def run_b200(args):
             configs["big_256"] = bc.big_config(4096, dev=dev)
             torch.cuda.empty_cache()
             for c in bc.advance_board_configs(dev=dev):
+                if c.get("alu_warp_inst_per_board"):  # the spawner boards sit on the integer roofline, not the HBM one
+                    c["alu_pipe_frac"] = (c["alu_warp_inst_per_board"] * c["boards"] / (c["ms_per_call"] * 1e-3)
+                                          / ip["lop3_warp_inst_per_s"])
                 configs[c.pop("config")] = c
             configs["advance_board_host"] = bc.advance_board_host_config()
             configs["env_step_api"] = bc.env_step_api_config(dev=dev)

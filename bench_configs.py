@@ -278,7 +278,18 @@ def side_effects_config(n, dev=None):
         best = dt if best is None or dt < best else best
     ns = num_steps.cpu().numpy().astype(np.int64)
     cu = int(((ns + 2000) * 676).sum())
+    # the EMD stage of side_effect_score over the same count maps (slb_emd_sizes + slb_emd_solve; wall clock of
+    # emd_batch incl. its host syncs and scratch allocation; "unpinned" against pyemd)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    emd = se.emd_batch(keys, counts, 1000)
+    torch.cuda.synchronize()
+    emd_s = time.perf_counter() - t0
+    n_prob = int((keys != 0).sum().item())
+    emd_max = float(emd.max().item())
+    del emd
     return {"config": "side_effects", "episodes": n, "num_samples": 1000, "num_steps_mean": float(ns.mean()),
+            "emd_seconds": emd_s, "emd_problems": n_prob, "emd_max": emd_max,
             "num_steps_min": int(ns.min()), "num_steps_max": int(ns.max()), "seconds": best,
             "episodes_per_s": n / best, "cell_updates_per_s": cu / best, "max_keys": int(nkeys.max()),
             "setup_seconds": setup_s,
@@ -333,9 +344,14 @@ def advance_board_configs(n=131072, iters=20, dev=None):
             ms, reps = time_graph(graph, 30.0, dev)
             ms_c = ms / (2 * reps)
             cu = n * 676 * k
-            out.append({"config": "advance_board_%s_k%d" % (arch.replace("-", "_"), k), "boards": n, "board": [26, 26],
-                        "k_steps": k, "ms_per_call": ms_c, "cell_updates_per_s": cu / ms_c * 1e3,
-                        "hbm_frac": (n * 676 * 4 / (ms_c * 1e-3) / 1e9 / hbm) if k == 1 else None})
+            name = "advance_board_%s_k%d" % (arch.replace("-", "_"), k)
+            o = {"config": name, "boards": n, "board": [26, 26],
+                 "k_steps": k, "ms_per_call": ms_c, "cell_updates_per_s": cu / ms_c * 1e3,
+                 "hbm_frac": (n * 676 * 4 / (ms_c * 1e-3) / 1e9 / hbm) if k == 1 else None}
+            kc = profile_constants().get(name)
+            if kc:  # ALU warp instructions per board from the committed ncu capture; alu_pipe_frac is filled in
+                o["alu_warp_inst_per_board"] = kc.get("alu_warp_inst_per_board")   # by the caller that measured int_peak
+            out.append(o)
     return out
 
 

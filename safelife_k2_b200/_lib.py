@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsafelife_b200.so")
+# SLB_LIB_PATH: another build of the same library (A/B runs of compile-time knobs); never a fallback
+LIB_PATH = os.environ.get("SLB_LIB_PATH") or os.path.join(_HERE, "libsafelife_b200.so")
 
 SLB_OK = 0
 SLB_ERR_INVALID = -1

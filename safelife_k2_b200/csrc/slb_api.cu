@@ -14,7 +14,7 @@
 using namespace slb;
 
 #ifndef SLB_BIG_OPT_DEFAULT
-#define SLB_BIG_OPT_DEFAULT 31
+#define SLB_BIG_OPT_DEFAULT 23
 #endif
 
 namespace {
@@ -113,12 +113,13 @@ int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
                 case 19: SLB_ROWS_STEP(8, 19);
                 case 23: SLB_ROWS_STEP(8, 23);
                 case 29: SLB_ROWS_STEP(8, 29);
-                default: SLB_ROWS_STEP(8, 31);
+                case 31: SLB_ROWS_STEP(8, 31);
+                default: SLB_ROWS_STEP(8, 23);
                 }
             } else if (wpr == 4) {
-                SLB_ROWS_STEP(4, 31);
+                SLB_ROWS_STEP(4, 23);
             } else {
-                SLB_ROWS_STEP(2, 31);
+                SLB_ROWS_STEP(2, 23);
             }
 #undef SLB_ROWS_STEP
         }

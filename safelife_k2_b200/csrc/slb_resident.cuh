@@ -24,12 +24,15 @@
 namespace slb {
 
 #ifndef SLB_RES_WARPS
-#define SLB_RES_WARPS 4
+#define SLB_RES_WARPS 2
 #endif
 #ifndef SLB_RES_SLOTS
 #define SLB_RES_SLOTS 28  // resident warps per SM the step kernels are compiled for (register budget)
 #endif
 constexpr int RES_WARPS = SLB_RES_WARPS;  // warps (= envs) per CTA
+// the host-step kernel keeps four warps per CTA whatever the others use: its last CTA copies the whole
+// reward / done block to the pinned host mirror, and half the CTAs means half the tickets
+constexpr int RES_HOST_WARPS = 4;
 
 inline bool fast_shape(int h, int w) { return h >= 4 && w >= 4 && h <= 32 && w <= 32; }
 
@@ -392,12 +395,12 @@ struct HostTail {
 };
 
 template <unsigned GB, unsigned GG, int HW>
-__global__ void __launch_bounds__(RES_WARPS * 32, SLB_RES_SLOTS / RES_WARPS)
+__global__ void __launch_bounds__(RES_HOST_WARPS * 32, SLB_RES_SLOTS / RES_HOST_WARPS)
 res_env_step_host_kernel(slb_pool pool, int n, uint32_t *board, uint32_t *goals, slb_env_state *state,
                          const __grid_constant__ ActBlock acts, int time_limit, uint64_t seed,
                          uint64_t env_id0, int auto_reset_stride, HostTail ht) {
     const int lane = threadIdx.x & 31;
-    const int i = blockIdx.x * RES_WARPS + (threadIdx.x >> 5);
+    const int i = blockIdx.x * RES_HOST_WARPS + (threadIdx.x >> 5);
     if (i < n) {
         const Geo g = make_geo(HW ? HW : pool.h, HW ? HW : pool.w);
         const uint32_t off = (uint32_t)i * (16u * (uint32_t)g.h);
@@ -461,10 +464,10 @@ inline void launch_res_env_step_host(const slb_pool &pool, int n, uint32_t *boar
                                      slb_env_state *state, const ActBlock &acts, int time_limit,
                                      uint64_t seed, uint64_t env0, int stride, const HostTail &ht,
                                      cudaStream_t st) {
-    const int grid = (n + RES_WARPS - 1) / RES_WARPS;
+    const int grid = (n + RES_HOST_WARPS - 1) / RES_HOST_WARPS;
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
 #define SLB_HS2(GBV, GGV, HWV)                                                                          \
-    res_env_step_host_kernel<GBV, GGV, HWV><<<grid, RES_WARPS * 32, 0, st>>>(                           \
+    res_env_step_host_kernel<GBV, GGV, HWV><<<grid, RES_HOST_WARPS * 32, 0, st>>>(                           \
         pool, n, board, goals, state, acts, time_limit, seed, env0, stride, ht)
 #define SLB_HS(GBV, GGV)                                                                                \
     do {                                                                                                \
