@@ -273,6 +273,17 @@ def run_b200(args):
         single = {"value": n * world / (ms1 / (r1 * 50) * 1e-3), "ms_per_step": ms1 / (r1 * 50),
                   "what": "ONE batch stepped back to back (dependent launches, state L2-resident)"}
 
+    # ---- informational: the ring with even / odd batches on two streams inside one graph (an actor that
+    # alternates two independent batches: one batch's load and drain overlap the other's compute).  Not the
+    # headline: `value` stays one stream, every launch ordered behind the previous one. ----
+    two = None
+    if not args.no_graph and ring >= 4:
+        L2n = ring - (ring % 2)
+        g2 = bc.capture2(lambda j, st: launch(j, st), L2n, dev)
+        ms2, r2 = bc.time_graph(g2, 20.0, dev, world)
+        two = {"streams": 2, "value": n * world / (ms2 / (r2 * L2n) * 1e-3), "ms_per_step": ms2 / (r2 * L2n),
+               "what": "same ring, even / odd batches on two streams inside one graph"}
+
     # ---- e2e: host-buffer steps through the public API (SafeLifeEnv.host_stepper -> slb_stepper_step / _wait) ----
     # Every step moves that step's actions from pinned host memory to the device (in the launch parameters),
     # runs the fused step and brings reward + done back to pinned host memory (written by the step's last
@@ -399,6 +410,8 @@ def run_b200(args):
     }
     if single is not None:
         line["single_batch"] = single
+    if two is not None:
+        line["two_stream_overlap"] = two
     if strong is not None:
         line["strong"] = strong
     if configs is not None:

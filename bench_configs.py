@@ -77,6 +77,23 @@ def capture(launch, L, dev):
     return graph
 
 
+def capture2(launch, L, dev):
+    """launch(j, cuda_stream_ptr) for j in 0..L-1 with even / odd j on two streams (fork / join inside one graph):
+    the launches must touch L different batches."""
+    side, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            s2.wait_stream(side)
+            for j in range(L):
+                launch(j, (side if j % 2 == 0 else s2).cuda_stream)
+            side.wait_stream(s2)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    return graph
+
+
 def time_graph(graph, min_ms=50.0, dev=None, world=1, tail=None, max_reps=200000):
     """Replays `graph` on the current stream until >= min_ms have passed (the repetition count is fixed before
     the timed region from one calibration replay; with several ranks every rank uses the largest count).
@@ -579,8 +596,18 @@ def strong_config(workload, total, rank, world, dev, min_ms=40.0, check_steps=12
 
     ms, reps = time_graph(graph, min_ms, dev, world, tail)
     ms_step = ms / (reps * L)
+    # informational: the same ring with even / odd batches on two streams (an actor that alternates two
+    # independent batches of its share); the judged figures above stay single-stream
+    two = None
+    if len(envs) >= 2:
+        L2n = len(envs) - (len(envs) % 2)
+        g2 = capture2(launch, L2n, dev)
+        ms2, r2 = time_graph(g2, min_ms / 2, dev, world)
+        two = {"ms_per_step": ms2 / (r2 * L2n), "env_steps_per_s": total / (ms2 / (r2 * L2n)) * 1e3}
+        del g2
     hbm, _ = hbm_peak()
     return {"workload": workload, "total_envs": total, "envs_per_gpu": n, "board": [h, w], "n_gpus": world,
+            "two_stream_overlap": two,
             "ms_per_step": ms_step, "env_steps_per_s": total / ms_step * 1e3,
             "cell_updates_per_s": total * 2 * h * w / ms_step * 1e3,
             "hbm_frac_algorithmic_per_gpu": n * (8 * h * w + 32) / (ms_step * 1e-3) / 1e9 / hbm,
@@ -627,6 +654,10 @@ def main():
             out.append(step_config("step_%s_%s" % (arch, cnt), lv, int(cnt), 26, 26, ms, consts=consts))
         if nm.startswith("big:"):
             out.append(big_config(int(nm.split(":")[1]), ms))
+    for nm in names:  # strong:<mixed_26|big_256>:<total> — one GPU's share of a strong-scaling job as a whole job
+        if nm.startswith("strong:"):
+            _, wl, tot = nm.split(":")
+            out.append(strong_config(wl, int(tot), 0, 1, torch.device("cuda", 0), ms))
     if "strong_mixed" in names:
         out.append(strong_config("mixed_26", 65536, 0, 1, torch.device("cuda", 0), ms))
     if "strong_big" in names:
