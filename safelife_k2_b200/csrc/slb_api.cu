@@ -14,7 +14,7 @@
 using namespace slb;
 
 #ifndef SLB_BIG_OPT_DEFAULT
-#define SLB_BIG_OPT_DEFAULT 23
+#define SLB_BIG_OPT_DEFAULT 55
 #endif
 
 namespace {
@@ -103,7 +103,14 @@ int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
 #define SLB_ROWS_STEP(WPR_, OPT_)                                                              \
     do {                                                                                       \
         if (int rc = allow_smem(big_rows_step_kernel<WPR_, OPT_>, bytes)) return rc;           \
-        big_rows_step_kernel<WPR_, OPT_><<<a.n, ROWS_THREADS, bytes, st>>>(*pool, a);          \
+        cudaLaunchAttribute attr_[1];                                                          \
+        attr_[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                      \
+        attr_[0].val.programmaticStreamSerializationAllowed = 1;                               \
+        cudaLaunchConfig_t cfg_ = {};                                                          \
+        cfg_.gridDim = dim3(a.n); cfg_.blockDim = dim3(ROWS_THREADS);                          \
+        cfg_.dynamicSmemBytes = bytes; cfg_.stream = st;                                       \
+        cfg_.attrs = attr_; cfg_.numAttrs = ((OPT_) & RO_PDL) ? 1 : 0;                         \
+        SLB_CUDA(cudaLaunchKernelEx(&cfg_, big_rows_step_kernel<WPR_, OPT_>, *pool, a));       \
         return SLB_OK;                                                                         \
     } while (0)
             if (wpr == 8) {
@@ -114,12 +121,13 @@ int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
                 case 23: SLB_ROWS_STEP(8, 23);
                 case 29: SLB_ROWS_STEP(8, 29);
                 case 31: SLB_ROWS_STEP(8, 31);
-                default: SLB_ROWS_STEP(8, 23);
+                case 55: SLB_ROWS_STEP(8, 55);
+                default: SLB_ROWS_STEP(8, 55);
                 }
             } else if (wpr == 4) {
-                SLB_ROWS_STEP(4, 23);
+                SLB_ROWS_STEP(4, 55);
             } else {
-                SLB_ROWS_STEP(2, 23);
+                SLB_ROWS_STEP(2, 55);
             }
 #undef SLB_ROWS_STEP
         }

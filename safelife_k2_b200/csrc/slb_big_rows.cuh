@@ -453,11 +453,12 @@ big_rows_env_kernel(slb_pool pool, BigArgs a) {
 //   RO_SCORE     when goals hold no spawner, current_points / performance_ratio are accumulated inside the
 //                goals' sliding window (new goal colours are in registers; the board's two plane groups are
 //                requested at the top of the body) instead of a separate pass that reloads both boards
+//   RO_PDL       programmatic dependent launch: see the griddepcontrol pair in rows_step_body
 // Always: slb_env_state lives in shared memory for the whole step (one 80-byte load, one store), the level's
 // exit mask is parked in shared memory while the physics runs, spawn ranks come from ONE CTA-wide scan (a
 // thread owns items / 256 consecutive items) instead of one scan per 256 items.
 // =====================================================================================================
-enum : int { RO_PREFETCH = 1, RO_HOIST = 2, RO_FIXB = 4, RO_SCORE = 8, RO_NEW = 16 };
+enum : int { RO_PREFETCH = 1, RO_HOIST = 2, RO_FIXB = 4, RO_SCORE = 8, RO_NEW = 16, RO_PDL = 32 };
 
 struct RowsAcc { int pts, cur, pos; };
 
@@ -655,9 +656,10 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
     const size_t words = (size_t)16 * items;
     uint32_t *board = a.board + i * words, *goals = a.goals + i * words;
     slb_env_state *st = a.state + i;
-    if (threadIdx.x < 5)
-        reinterpret_cast<uint4 *>(&shst)[threadIdx.x] = reinterpret_cast<const uint4 *>(st)[threadIdx.x];
-    if (threadIdx.x == 32) sh_act = a.actions[i];
+    // RO_PDL (the launch carries the programmatic-serialization attribute): the next launch on the stream may
+    // take SM slots as ours free up; its CTAs request their env's lines into L2 and then wait for this grid to
+    // complete before their first read (L2 is the point of coherence: a prefetched line reads back current)
+    if (OPT & RO_PDL) asm volatile("griddepcontrol.launch_dependents;");
     if (OPT & RO_PREFETCH) {  // 128-byte lines of the groups that exist: items / 8 lines per group
         const int lpg = items >> 3;
         for (int k = threadIdx.x; k < 4 * lpg; k += ROWS_THREADS) {
@@ -666,6 +668,10 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
             if (gg & grp) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(goals) + (size_t)k * 128));
         }
     }
+    if (OPT & RO_PDL) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x < 5)
+        reinterpret_cast<uint4 *>(&shst)[threadIdx.x] = reinterpret_cast<const uint4 *>(st)[threadIdx.x];
+    if (threadIdx.x == 32) sh_act = a.actions[i];
     __syncthreads();
     const int level = shst.level_id;
     const uint64_t env = a.env_id0 + (uint64_t)i;
