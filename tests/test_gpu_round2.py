@@ -266,6 +266,50 @@ def test_sliding_window_step_every_row_width(sl, h, w, spawner_goals):
     _run_vs_oracle(sl, lv, 8, 40, seed=7, auto_reset=True, time_limit=17, every=8)
 
 
+@pytest.mark.parametrize("shape", ["26x26", "256x256"])
+def test_two_batches_on_two_streams(sl, shape):
+    """The actor pattern of INTEGRATION.md §4: two independent env batches stepped on two CUDA streams with their
+    launches interleaved (and overlapping on the GPU); each batch equals the oracle, i.e. no kernel keeps state
+    outside the buffers it is given."""
+    if shape == "26x26":
+        lv, n, steps = gu.levels("prune-spawn"), 2048, 40
+    else:
+        lv, n, steps = _random_levels(np.random.RandomState(77), 4, 256, 256, exits=8), 24, 12
+    pool = sl.game.LevelPool(lv)
+    P = pool.n_levels
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    envs, oracles = [], []
+    for b in range(2):
+        e = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=1000 * b, global_counter=None, compute_obs=False,
+                               auto_reset=False, time_limit=1000)
+        e.seed(3)
+        e.reset()
+        envs.append(e)
+        oracles.append(slo.OracleBatchEnv(slo.OraclePool(**lv), (np.arange(n) + 1000 * b) % P, seed=3, env_id0=1000 * b,
+                                          threads=8, time_limit=1000))
+    torch.cuda.synchronize()
+    rng = np.random.RandomState(9)
+    acts = rng.randint(9, size=(steps, 2, n))
+    dev_acts = torch.from_numpy(acts.astype(np.uint8)).cuda()
+    rewards = [[], []]
+    torch.cuda.synchronize()
+    for t in range(steps):                      # no host synchronisation inside the loop
+        for b in range(2):
+            with torch.cuda.stream(streams[b]):
+                _, r, d, _ = envs[b].step(dev_acts[t, b])
+                rewards[b].append(r)
+    torch.cuda.synchronize()
+    for b in range(2):
+        want = np.stack([oracles[b].step(acts[t, b])[0] for t in range(steps)])
+        got = torch.stack(rewards[b]).cpu().numpy()
+        assert (got == want).all(), b
+        assert (envs[b].game.board.cpu().numpy() == oracles[b].boards).all(), b
+        assert (envs[b].game.goals.cpu().numpy() == oracles[b].goals).all(), b
+        st = envs[b].game.state_numpy()
+        for f in st.dtype.names:
+            assert (st[f] == oracles[b].states[f]).all(), (b, f)
+
+
 @pytest.mark.parametrize("archive", gu.ARCHIVES)
 def test_soak_every_archive(sl, archive):
     """Bounded soak: 64 envs x 300 steps of every v1.0 archive with and without auto-reset against the oracle,
