@@ -291,7 +291,7 @@ def run_b200(args):
     # loop: while one batch's results travel back, the next batches step); each step's outputs are waited
     # for before that batch's buffers are reused.
     e2e_steps = max(20000, min(K, 100000))  # >= 20 000 steps (~0.1 s of wall clock) whatever K is
-    depth = int(os.environ.get("SLB_BENCH_DEPTH", "6"))
+    depth = int(os.environ.get("SLB_BENCH_DEPTH", "7"))
     h_act = torch.from_numpy(rng.randint(9, size=(n_act, n)).astype(np.uint8)).pin_memory()
     h_out = [torch.zeros(5 * n, dtype=torch.uint8).pin_memory() for _ in range(depth)]
     streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]

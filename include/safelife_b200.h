@@ -226,7 +226,7 @@ int slb_env_step_host(const slb_pool *pool, int n, void *d_board, void *d_goals,
                       int auto_reset_stride, void *stream);
 
 /* The same without the final wait: H2D copy, step and D2H copy are queued on `stream` (give steps that
- * should overlap their own streams; at most 8 streams with a step in flight per calling thread).  h_actions is consumed
+ * should overlap their own streams; at most 16 streams with a step in flight per calling thread).  h_actions is consumed
  * before the call returns; h_reward / h_done are valid only after slb_stream_wait(stream), called from
  * the SAME host thread, returns (a plain cudaStreamSynchronize is not enough: on a non-default stream
  * the step goes through a page-locked staging block inside the library and slb_stream_wait hands the

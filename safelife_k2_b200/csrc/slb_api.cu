@@ -647,7 +647,8 @@ struct HostIo {
     volatile uint32_t *pend_flag;  // direct path: the host word the step's last CTA publishes `pend_seq` to
     uint32_t pend_seq, seq;
 };
-thread_local HostIo g_slots[8] = {};
+constexpr int kMaxSlots = 16;  // streams with a host step in flight per calling thread
+thread_local HostIo g_slots[kMaxSlots] = {};
 thread_local int g_slots_used = 0;
 
 int finish_pending(HostIo *s);
@@ -668,14 +669,14 @@ void release_slot(HostIo *s) {
 int host_io_slot(cudaStream_t st, size_t need, HostIo **out) {
     HostIo *s = find_slot(st);
     if (!s) {
-        if (g_slots_used < 8) {
+        if (g_slots_used < kMaxSlots) {
             s = &g_slots[g_slots_used++];
         } else {
             // all slots taken: recycle the one used longest ago that has no step in flight (streams come
             // and go in a long-running process; a destroyed stream's slot is idle by construction)
-            for (int k = 0; k < 8; k++)
+            for (int k = 0; k < kMaxSlots; k++)
                 if (!g_slots[k].pend_n && (!s || g_slots[k].last_use < s->last_use)) s = &g_slots[k];
-            if (!s) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 8 streams with a step in flight on one thread");
+            if (!s) return fail(SLB_ERR_UNSUPPORTED, "slb_env_step_host: more than 16 streams with a step in flight on one thread");
             release_slot(s);
         }
         memset(s, 0, sizeof(*s));

@@ -662,11 +662,11 @@ def test_step_host_many_streams(sl):
         e.seed(4); e.reset()
     rng = np.random.RandomState(0)
     r = np.zeros(n, np.int32); d = np.zeros(n, np.uint8)
-    streams = [torch.cuda.Stream() for _ in range(12)]
-    for t in range(36):
+    streams = [torch.cuda.Stream() for _ in range(20)]   # 16 slots per thread
+    for t in range(60):
         acts = rng.randint(9, size=n).astype(np.uint8)
-        st = streams[t % 12]
-        st.wait_stream(streams[(t - 1) % 12])
+        st = streams[t % 20]
+        st.wait_stream(streams[(t - 1) % 20])
         a.step_host(acts, r, d, sync=False, stream=st)
         a.wait(st)
         _, rb, db, _ = b.step(acts)
