@@ -66,6 +66,7 @@ SYMBOLS = {
     "slb_stepper_step": (_i, [_vp, _vp, _vp, _vp]),
     "slb_stepper_wait": (_i, [_vp]),
     "slb_stepper_destroy": (None, [_vp]),
+    "slb_stepper_bind_outputs": (_i, [_vp, _vp, _vp]),
     "slb_side_effect_counts": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _vp, _u64, _u64, _vp, _i, _vp,
                                     _vp, _vp, _vp, _vp]),
     "slb_accumulate_stats": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
@@ -103,7 +104,7 @@ def load():
             fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
             fn.restype = res
             fn.argtypes = args
-        if lib.slb_abi_version() != 4:
+        if lib.slb_abi_version() != 5:
             raise ImportError("libsafelife_b200.so ABI version mismatch")
         _lib = lib
     return _lib

@@ -781,7 +781,7 @@ int build_step_graph(HostIo *s, const StepKey &k, cudaGraphExec_t *exec) {
 // `own`: the caller's graph (a stepper's), or NULL to use the slot's cache
 int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
               const uint8_t *h_actions, int time_limit, uint64_t seed, uint64_t env_id0, int32_t *h_reward,
-              uint8_t *h_done, int auto_reset_stride, void *stream, StepGraph *own) {
+              uint8_t *h_done, int auto_reset_stride, void *stream, StepGraph *own, uint8_t *bound_dev = nullptr) {
     if (n < 0 || !h_actions) return fail(SLB_ERR_INVALID, "slb_env_step_host: bad arguments");
     if (n == 0) return SLB_OK;
     if (int rc = check_pool(pool)) return rc;
@@ -808,12 +808,16 @@ int host_step(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env
         ht.d_reward = (int32_t *)d_io; ht.d_done = d_io + off_done;
         ht.counter = (unsigned *)(s->d - kIoHeader);
         ht.h_block = s->h; ht.h_seq = (uint32_t *)(s->h - kIoHeader);
+        // outputs bound with slb_stepper_bind_outputs: the last CTA writes straight into the caller's page-locked
+        // block [reward 4n | done n] and the copy out of the slot's mirror is skipped
+        const bool zero_copy = bound_dev != nullptr;
+        if (zero_copy) ht.h_block = bound_dev;
         ht.seq = ++s->seq;
         if (ht.seq == 0) ht.seq = ++s->seq;  // 0 is the freshly allocated block's value
         launch_res_env_step_host(*pool, n, (uint32_t *)d_board, (uint32_t *)d_goals, d_state, acts, time_limit,
                                  seed, env_id0, auto_reset_stride, ht, st);
         SLB_LAUNCHED();
-        s->pend_reward = h_reward; s->pend_done = h_done; s->pend_n = n;
+        s->pend_reward = zero_copy ? nullptr : h_reward; s->pend_done = zero_copy ? nullptr : h_done; s->pend_n = n;
         s->pend_flag = (volatile uint32_t *)ht.h_seq; s->pend_seq = ht.seq;
         return SLB_OK;
     }
@@ -906,6 +910,8 @@ struct slb_stepper {
     void *stream;
     int device;  // current device at creation; made current again by every step (callers hop devices)
     StepGraph graph;
+    int32_t *bound_reward;  // slb_stepper_bind_outputs: the caller's page-locked output block and its device address
+    uint8_t *bound_dev;
 };
 
 int slb_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals, slb_env_state *d_state,
@@ -917,7 +923,7 @@ int slb_stepper_create(const slb_pool *pool, int n, void *d_board, void *d_goals
     int dev = 0;
     SLB_CUDA(cudaGetDevice(&dev));
     slb_stepper *s = new slb_stepper{pool, n, time_limit, auto_reset_stride, d_board, d_goals, d_state,
-                                     seed, env_id0, stream, dev, {}};
+                                     seed, env_id0, stream, dev, {}, nullptr, nullptr};
     memset(&s->graph, 0, sizeof(s->graph));
     *out = s;
     return SLB_OK;
@@ -927,8 +933,31 @@ int slb_stepper_step(slb_stepper *s, const uint8_t *h_actions, int32_t *h_reward
     if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
     int dev = s->device;
     if (cudaGetDevice(&dev) == cudaSuccess && dev != s->device) SLB_CUDA(cudaSetDevice(s->device));
+    uint8_t *zc = (s->bound_dev && h_reward == s->bound_reward && h_done == (uint8_t *)(h_reward + s->n)) ? s->bound_dev
+                                                                                                       : nullptr;
     return host_step(s->pool, s->n, s->board, s->goals, s->state, h_actions, s->time_limit, s->seed,
-                     s->env_id0, h_reward, h_done, s->stride, s->stream, &s->graph);
+                     s->env_id0, h_reward, h_done, s->stride, s->stream, &s->graph, zc);
+}
+
+int slb_stepper_bind_outputs(slb_stepper *s, int32_t *h_reward, uint8_t *h_done) {
+    if (!s) return fail(SLB_ERR_INVALID, "stepper is NULL");
+    s->bound_reward = nullptr; s->bound_dev = nullptr;
+    if (!h_reward && !h_done) return SLB_OK;  // unbind
+    const size_t bytes = (size_t)5 * s->n;
+    if (!h_reward || h_done != (uint8_t *)(h_reward + s->n) || (s->n & 15) || ((uintptr_t)h_reward & 15))
+        return fail(SLB_ERR_INVALID, "slb_stepper_bind_outputs: the outputs must be ONE 16-byte aligned block "
+                    "[int32 reward x n | uint8 done x n] with n a multiple of 16");
+    cudaPointerAttributes a0, a1;
+    if (cudaPointerGetAttributes(&a0, h_reward) != cudaSuccess ||
+        cudaPointerGetAttributes(&a1, (const char *)h_reward + bytes - 1) != cudaSuccess ||
+        a0.type != cudaMemoryTypeHost || a1.type != cudaMemoryTypeHost || !a0.devicePointer) {
+        cudaGetLastError();
+        return fail(SLB_ERR_INVALID, "slb_stepper_bind_outputs: the block is not page-locked host memory "
+                    "(cudaHostAlloc / cudaHostRegister / torch pin_memory)");
+    }
+    s->bound_reward = h_reward;
+    s->bound_dev = (uint8_t *)a0.devicePointer;
+    return SLB_OK;
 }
 
 int slb_stepper_wait(slb_stepper *s) {

@@ -46,6 +46,12 @@ class HostStepper(object):
         if rc:
             _lib.check(rc)
 
+    def bind_outputs(self, reward_ptr, done_ptr):
+        """The outputs of later step(a, reward_ptr, done_ptr) calls are one page-locked block [int32 reward x n |
+        uint8 done x n] (e.g. a torch pin_memory() uint8 tensor of 5 n bytes, n a multiple of 16) that stays alive:
+        the step then writes them there directly (slb_stepper_bind_outputs).  None, None unbinds."""
+        _lib.check(self._env._lib.slb_stepper_bind_outputs(self._sp, reward_ptr, done_ptr))
+
 
 class _Info(dict):
     """The step's info dict (safelife_env.py:176-186): 'board', 'goals' (uint16 [N,H,W] tensors exported

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "libsafelife_b200.so does not export %s" % n
     assert sorted(_lib.SYMBOLS) == names, "python binding table out of sync with the header"
-    assert _lib.load().slb_abi_version() == 4
+    assert _lib.load().slb_abi_version() == 5
 
 
 def test_env_state_layout_matches_header():

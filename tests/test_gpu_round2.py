@@ -310,6 +310,45 @@ def test_two_batches_on_two_streams(sl, shape):
             assert (st[f] == oracles[b].states[f]).all(), (b, f)
 
 
+def test_stepper_bound_outputs(sl):
+    """slb_stepper_bind_outputs: with the outputs bound to one page-locked block the step writes them there
+    directly; rewards / dones / state equal an env stepped the ordinary way, with other pointers the stepper works
+    as before, and a block that is not page-locked (or not of the required shape) is refused."""
+    lv = gu.levels("prune-spawn")
+    pool = sl.game.LevelPool(lv)
+    n = 192
+    a = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False, auto_reset=True, time_limit=9)
+    b = sl.env.SafeLifeEnv(pool, num_envs=n, global_counter=None, compute_obs=False, auto_reset=True, time_limit=9)
+    for e in (a, b):
+        e.seed(6); e.reset()
+    st = torch.cuda.Stream()
+    hs = a.host_stepper(st)
+    out = torch.full((5 * n,), 0xAB, dtype=torch.uint8).pin_memory()
+    other = np.zeros(5 * n, np.uint8)
+    hs.bind_outputs(out.data_ptr(), out.data_ptr() + 4 * n)
+    rng = np.random.RandomState(3)
+    acts = torch.from_numpy(rng.randint(9, size=(30, n)).astype(np.uint8)).pin_memory()
+    for t in range(30):
+        if t % 5 == 4:   # other pointers: through the library's mirror, as before
+            hs.step(acts[t].data_ptr(), other.ctypes.data, other.ctypes.data + 4 * n)
+            hs.wait()
+            r, d = other[:4 * n].view(np.int32), other[4 * n:]
+        else:
+            hs.step(acts[t].data_ptr(), out.data_ptr(), out.data_ptr() + 4 * n)
+            hs.wait()
+            r, d = out[:4 * n].view(torch.int32).numpy(), out[4 * n:].numpy()
+        _, rb, db, _ = b.step(acts[t].numpy())
+        assert (r == rb.cpu().numpy()).all() and (d == db.cpu().numpy()).all(), t
+    assert (a.game.state == b.game.state).all() and (a.game.board == b.game.board).all()
+    with pytest.raises(sl.lib.SlbError):
+        hs.bind_outputs(other.ctypes.data, other.ctypes.data + 4 * n)              # pageable memory
+    with pytest.raises(sl.lib.SlbError):
+        hs.bind_outputs(out.data_ptr(), out.data_ptr() + 4 * n - 16)               # not one [reward | done] block
+    hs.bind_outputs(None, None)                                                     # unbind
+    hs.step(acts[0].data_ptr(), out.data_ptr(), out.data_ptr() + 4 * n)
+    hs.wait()
+
+
 @pytest.mark.parametrize("archive", gu.ARCHIVES)
 def test_soak_every_archive(sl, archive):
     """Bounded soak: 64 envs x 300 steps of every v1.0 archive with and without auto-reset against the oracle,
