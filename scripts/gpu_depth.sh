@@ -1,15 +1,15 @@
 #!/bin/bash
 O=gpurun_out
-(echo '{"variant": "4 CTAs/SM, kfirst 8 (default)"}'; python bench_configs.py side_effects
- echo '{"variant": "4 CTAs/SM, kfirst 6"}'; SLB_SIDE_KFIRST=6 python bench_configs.py side_effects
- echo '{"variant": "5 CTAs/SM (89 regs), kfirst 6"}'; SLB_SIDE_KFIRST=6 SLB_LIB_PATH=scripts/_alt/libsafelife_b200_side5.so python bench_configs.py side_effects
- echo '{"variant": "5 CTAs/SM (89 regs), kfirst 8"}'; SLB_LIB_PATH=scripts/_alt/libsafelife_b200_side5.so python bench_configs.py side_effects
- echo '{"variant": "5 CTAs/SM (89 regs), kfirst 7"}'; SLB_SIDE_KFIRST=7 SLB_LIB_PATH=scripts/_alt/libsafelife_b200_side5.so python bench_configs.py side_effects) > $O/c22_side.jsonl 2>&1
+python -m pytest tests -x -q -m gpu -k "emd or no_alloc or side_effect_score" > $O/c23_tests.log 2>&1; tail -2 $O/c23_tests.log
+SLB_EMD_BITS=0 python -m pytest tests -x -q -m gpu -k "emd or no_alloc" > $O/c23_tests_nobits.log 2>&1; tail -1 $O/c23_tests_nobits.log
+(echo '{"variant": "cached minimum + flow bits"}'; python bench_configs.py side_effects
+ echo '{"variant": "cached minimum only (SLB_EMD_BITS=0)"}'; SLB_EMD_BITS=0 python bench_configs.py side_effects) > $O/c23_emd.jsonl 2>&1
+python scripts/profile_kernels.py emd 2>&1 | tail -2
+SLB_EMD_BITS=0 python scripts/profile_kernels.py emd 2>&1 | tail -2
 python - <<'PY'
 import json
-for l in open("gpurun_out/c22_side.jsonl"):
+for l in open("gpurun_out/c23_emd.jsonl"):
     try: d = json.loads(l)
     except Exception: print(l[:200]); continue
-    print({k: d[k] for k in d if k in ("variant", "seconds", "episodes_per_s", "max_keys")})
+    print({k: d[k] for k in d if k in ("variant", "seconds", "emd_seconds", "emd_problems", "emd_max")})
 PY
-SLB_SIDE_KFIRST=6 SLB_LIB_PATH=scripts/_alt/libsafelife_b200_side5.so python -m pytest tests -x -q -m gpu -k "side_effect or soak" > $O/c22_tests.log 2>&1; tail -2 $O/c22_tests.log
