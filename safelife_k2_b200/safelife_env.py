@@ -202,7 +202,7 @@ class SafeLifeEnv(object):
         self._seed = 0
         self._lib = _lib.load()
         self._steppers = {}
-        self._dev_sp, self._dev_key, self._obs_shape = None, None, None
+        self._dev_sp, self._dev_key, self._dev_cur, self._obs_shape = None, None, None, None
         self._obs_scratch = False
         self._fused_obs = True
         self._dev_index = self.pool.device.index if self.pool.device.index is not None else torch.cuda.current_device()
@@ -257,7 +257,7 @@ class SafeLifeEnv(object):
         if d.get("global_counter") is not None and self.global_counter is not None:
             for k, v in d["global_counter"].items():
                 setattr(self.global_counter, k, v)
-        self._dev_key = None  # rebind the native steppers (the seed may have changed)
+        self._dev_key = self._dev_cur = None  # rebind the native steppers (the seed may have changed)
         self._drop_steppers()
 
     # ------------------------------------------------------------------------------------------
@@ -351,10 +351,15 @@ class SafeLifeEnv(object):
         st = _raw_stream(self._dev_index)
         # every argument that does not change from step to step is bound once in a native stepper
         oc = self.output_channels
-        key = (id(g), self.time_limit, g.seed, self.auto_reset, self.view_shape, tuple(oc) if oc else None,
-               self.remove_white_goals, self.compute_obs, self._fused_obs, self.global_counter is not None)
-        if key != self._dev_key:
-            self._bind_dev_stepper(key)
+        # (compared by identity / equality against the values the stepper was bound with: no tuple(oc) per step)
+        cur = (g, self.time_limit, g.seed, self.auto_reset, self.view_shape, oc, self.remove_white_goals,
+               self.compute_obs, self._fused_obs, self.global_counter is not None)
+        if cur != self._dev_cur:
+            key = (id(g), self.time_limit, g.seed, self.auto_reset, self.view_shape, tuple(oc) if oc else None,
+                   self.remove_white_goals, self.compute_obs, self._fused_obs, self.global_counter is not None)
+            if key != self._dev_key:
+                self._bind_dev_stepper(key)
+            self._dev_cur = cur[:5] + (list(oc) if isinstance(oc, list) else oc,) + cur[6:]
         dev = self.pool.device
         done = torch.empty(g.n, dtype=torch.bool, device=dev)  # the step writes 0 / 1; fresh every step
         reward = torch.empty(g.n, dtype=torch.int32, device=dev)
@@ -365,7 +370,9 @@ class SafeLifeEnv(object):
         if rc == _lib.SLB_ERR_UNSUPPORTED and obs is not None:
             # this board / view shape has no fused step + observation: step, then get_obs
             self._fused_obs = False
-            self._bind_dev_stepper(key[:8] + (False,) + key[9:])
+            k0 = self._dev_key
+            self._bind_dev_stepper(k0[:8] + (False,) + k0[9:])
+            self._dev_cur = None
             obs = None
             rc = self._dev_step(self._dev_sp, acts.data_ptr(), reward.data_ptr(), done.data_ptr(), None, st)
         if rc:
@@ -463,7 +470,7 @@ class SafeLifeEnv(object):
         self._steppers.clear()
         if self._dev_sp is not None:
             self._lib.slb_dev_stepper_destroy(self._dev_sp)
-            self._dev_sp, self._dev_key = None, None
+            self._dev_sp, self._dev_key, self._dev_cur = None, None, None
 
     def __del__(self):
         try:
