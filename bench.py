@@ -154,7 +154,8 @@ def run_reference(args):
     n_envs = ENVS_PER_GPU
     _, dt0, _, _ = cpu_arm(n_envs, max(4, args.warmup), 1, threads)   # calibrate (also the warm-up)
     per = dt0 / max(4, args.warmup)
-    inner = int(max(1, min(2000, round(10.0 / (per * args.steps)))))
+    budget = float(os.environ.get("SLB_REF_SECONDS", "10"))  # seconds of CPU work in the timed sample
+    inner = int(max(1, min(2000, round(budget / (per * args.steps)))))
     value, dt, kind, physics = cpu_arm(n_envs, args.steps * inner, args.warmup, threads)
     sample = ("%d x %d env-steps of one %d-env append-still batch (%.1f s of wall clock on %d threads); physics = %s, "
               "rules = C port of safelife_game.py" % (args.steps, inner, n_envs, dt, threads, physics))

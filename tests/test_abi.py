@@ -125,3 +125,24 @@ def test_every_product_module_imports_without_a_gpu():
         importlib.import_module("safelife_k2_b200." + m)
     for f in ("bench.py", "bench_configs.py", "__graft_entry__.py", "scripts/sanitize_paths.py"):
         py_compile.compile(os.path.join(ROOT, f), doraise=True)
+
+
+def test_bench_reference_arm_line():
+    """`bench.py --impl reference` (the CPU arm the driver runs beside the GPU arm): one JSON line with the contract's
+    keys, timed on the oracle's CPU path (no GPU needed).  SLB_REF_SECONDS keeps the sample short here."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, SLB_REF_SECONDS="1.5")
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "3",
+                          "--warmup", "1"], capture_output=True, text=True, timeout=300, env=env, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "env_steps_per_s" and d["unit"] == "env-steps/s"
+    assert d["higher_is_better"] is True and d["steps"] == 3 and d["value"] > 0
+    assert d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["envs_per_gpu"] == 4096 and d["config"]["board"] == [26, 26]

@@ -266,6 +266,44 @@ def test_sliding_window_step_every_row_width(sl, h, w, spawner_goals):
     _run_vs_oracle(sl, lv, 8, 40, seed=7, auto_reset=True, time_limit=17, every=8)
 
 
+@pytest.mark.parametrize("shape", ["26x26", "256x256", "128x128"])
+def test_back_to_back_launches_without_host_sync(sl, shape):
+    """Dependent step launches queued back to back on one stream (no host synchronisation in between): the
+    programmatic-dependent-launch kernels start before their predecessor has finished and must not read its
+    outputs early.  Every step's rewards / dones and the final state against the oracle."""
+    if shape == "26x26":
+        lv, n, steps = gu.levels("append-spawn"), 4096, 48
+    elif shape == "256x256":
+        lv, n, steps = _random_levels(np.random.RandomState(31), 4, 256, 256, exits=8), 40, 16
+    else:
+        lv, n, steps = _random_levels(np.random.RandomState(32), 4, 128, 128, exits=8), 40, 16
+    pool = sl.game.LevelPool(lv)
+    P = pool.n_levels
+    env = sl.env.SafeLifeEnv(pool, num_envs=n, env_id0=7, global_counter=None, compute_obs=False, auto_reset=False,
+                             time_limit=1000)
+    env.seed(8)
+    env.reset()
+    o = slo.OracleBatchEnv(slo.OraclePool(**lv), (np.arange(n) + 7) % P, seed=8, env_id0=7, threads=8, time_limit=1000)
+    acts = np.random.RandomState(5).randint(9, size=(steps, n))
+    dev_acts = torch.from_numpy(acts.astype(np.uint8)).cuda()
+    torch.cuda.synchronize()
+    rs, ds = [], []
+    for t in range(steps):
+        _, r, d, _ = env.step(dev_acts[t])
+        rs.append(r)
+        ds.append(d)
+    torch.cuda.synchronize()
+    got_r, got_d = torch.stack(rs).cpu().numpy(), torch.stack(ds).cpu().numpy()
+    for t in range(steps):
+        orr, od = o.step(acts[t])
+        assert (got_r[t] == orr).all() and (got_d[t] == (od != 0)).all(), t
+    assert (env.game.board.cpu().numpy() == o.boards).all()
+    assert (env.game.goals.cpu().numpy() == o.goals).all()
+    st = env.game.state_numpy()
+    for f in st.dtype.names:
+        assert (st[f] == o.states[f]).all(), f
+
+
 @pytest.mark.parametrize("shape", ["26x26", "256x256"])
 def test_two_batches_on_two_streams(sl, shape):
     """The actor pattern of INTEGRATION.md §4: two independent env batches stepped on two CUDA streams with their
