@@ -102,13 +102,14 @@ int launch_big(const slb_pool *pool, BigArgs a, cudaStream_t st) {
         if (a.ops == (BIG_ACTION | BIG_PHYSICS | BIG_BOOK) && opt != 0) {
 #define SLB_ROWS_STEP(WPR_, OPT_)                                                              \
     do {                                                                                       \
-        if (int rc = allow_smem(big_rows_step_kernel<WPR_, OPT_>, bytes)) return rc;           \
+        const size_t sbytes_ = rows_step_smem_bytes(pool->h, pool->w);                         \
+        if (int rc = allow_smem(big_rows_step_kernel<WPR_, OPT_>, sbytes_)) return rc;         \
         cudaLaunchAttribute attr_[1];                                                          \
         attr_[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                      \
         attr_[0].val.programmaticStreamSerializationAllowed = 1;                               \
         cudaLaunchConfig_t cfg_ = {};                                                          \
         cfg_.gridDim = dim3(a.n); cfg_.blockDim = dim3(ROWS_THREADS);                          \
-        cfg_.dynamicSmemBytes = bytes; cfg_.stream = st;                                       \
+        cfg_.dynamicSmemBytes = sbytes_; cfg_.stream = st;                                     \
         cfg_.attrs = attr_; cfg_.numAttrs = ((OPT_) & RO_PDL) ? 1 : 0;                         \
         SLB_CUDA(cudaLaunchKernelEx(&cfg_, big_rows_step_kernel<WPR_, OPT_>, *pool, a));       \
         return SLB_OK;                                                                         \

@@ -20,7 +20,10 @@
 
 namespace slb {
 
-constexpr int ROWS_THREADS = 256;
+#ifndef SLB_ROWS_THREADS
+#define SLB_ROWS_THREADS 256
+#endif
+constexpr int ROWS_THREADS = SLB_ROWS_THREADS;  // (a compile-time knob for A/B builds: 128 = four CTAs' worth of registers per SM)
 
 inline bool rows_shape(int h, int w) {
     if (w != 64 && w != 128 && w != 256) return false;
@@ -29,9 +32,17 @@ inline bool rows_shape(int h, int w) {
 }
 
 // 6 words per item for the spawn draws + the 11 source planes of every thread's bottom halo row
-// ... + four 16-byte staging slots per thread for the step kernel's asynchronous row copies
+// (the all-stages kernel; its rank array and draw words are per item)
 __host__ __device__ inline size_t rows_smem_bytes(int h, int w) {
     return ((size_t)6 * h * (w / 32) + (size_t)12 * ROWS_THREADS + (size_t)16 * ROWS_THREADS) * 4;
+}
+// The step kernel: five words per item (eligible word, parked exit mask, three spawn colours), the halo block, and
+// ONE region that is the threads' staging slots while the window slides (four 16-byte slots per thread) and the
+// packed draw outcomes afterwards (one bit per eligible cell: at most one word per item) — 54 KB at 256 x 256
+// with 128 threads, so that four CTAs fit an SM.
+__host__ __device__ inline size_t rows_step_smem_bytes(int h, int w) {
+    const size_t items = (size_t)h * (w / 32), stage = (size_t)16 * ROWS_THREADS;
+    return ((size_t)5 * items + (size_t)12 * ROWS_THREADS + (stage > items ? stage : items)) * 4;
 }
 
 struct RowsSmem {
@@ -431,7 +442,7 @@ big_env_kernel(slb_pool pool, BigArgs a) {
 }
 
 template <int WPR>
-__global__ void __launch_bounds__(ROWS_THREADS, 2)
+__global__ void __launch_bounds__(ROWS_THREADS, 512 / ROWS_THREADS)
 big_rows_env_kernel(slb_pool pool, BigArgs a) {
     extern __shared__ __align__(16) uint32_t big_smem[];
     big_env_body<WPR>(pool, a, big_smem);
@@ -648,8 +659,9 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
     const int items = g.items;
     RowsSmem rs;
     rs.elig = big_smem; rs.rank = rs.elig + items; rs.tr = rs.rank + items; rs.tg = rs.tr + items;
-    rs.tb = rs.tg + items; rs.draws = rs.tb + items; rs.halo = rs.draws + items;
+    rs.tb = rs.tg + items; rs.halo = rs.tb + items;
     rs.stage = rs.halo + 12 * ROWS_THREADS;  // (11 halo planes, padded to keep the slots 16-byte aligned)
+    rs.draws = rs.stage;  // the draws are evaluated after the window's last staged row has been taken
     rs.warp_tot = warp_tot;
     uint32_t *sh_e0 = rs.rank;  // (the single scan keeps ranks in registers: this array parks the exit mask)
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
@@ -754,7 +766,7 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
 }
 
 template <int WPR, int OPT>
-__global__ void __launch_bounds__(ROWS_THREADS, 2)
+__global__ void __launch_bounds__(ROWS_THREADS, 512 / ROWS_THREADS)
 big_rows_step_kernel(slb_pool pool, BigArgs a) {
     extern __shared__ __align__(16) uint32_t big_smem[];
     rows_step_body<WPR, OPT>(pool, a, big_smem);
