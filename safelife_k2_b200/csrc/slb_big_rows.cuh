@@ -36,13 +36,12 @@ inline bool rows_shape(int h, int w) {
 __host__ __device__ inline size_t rows_smem_bytes(int h, int w) {
     return ((size_t)6 * h * (w / 32) + (size_t)12 * ROWS_THREADS + (size_t)16 * ROWS_THREADS) * 4;
 }
-// The step kernel: five words per item (eligible word, parked exit mask, three spawn colours), the halo block, and
+// The step kernel: four words per item (eligible word, three spawn colours), the halo block, and
 // ONE region that is the threads' staging slots while the window slides (four 16-byte slots per thread) and the
-// packed draw outcomes afterwards (one bit per eligible cell: at most one word per item) — 54 KB at 256 x 256
-// with 128 threads, so that four CTAs fit an SM.
+// packed draw outcomes afterwards (one bit per eligible cell: at most one word per item) — 60 KB at 256 x 256.
 __host__ __device__ inline size_t rows_step_smem_bytes(int h, int w) {
     const size_t items = (size_t)h * (w / 32), stage = (size_t)16 * ROWS_THREADS;
-    return ((size_t)5 * items + (size_t)12 * ROWS_THREADS + (stage > items ? stage : items)) * 4;
+    return ((size_t)4 * items + (size_t)12 * ROWS_THREADS + (stage > items ? stage : items)) * 4;
 }
 
 struct RowsSmem {
@@ -658,12 +657,12 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
     const BigGeo g = big_geo(pool.h, pool.w);
     const int items = g.items;
     RowsSmem rs;
-    rs.elig = big_smem; rs.rank = rs.elig + items; rs.tr = rs.rank + items; rs.tg = rs.tr + items;
+    // (the single scan keeps ranks in registers: no rank array here)
+    rs.elig = big_smem; rs.rank = nullptr; rs.tr = rs.elig + items; rs.tg = rs.tr + items;
     rs.tb = rs.tg + items; rs.halo = rs.tb + items;
     rs.stage = rs.halo + 12 * ROWS_THREADS;  // (11 halo planes, padded to keep the slots 16-byte aligned)
     rs.draws = rs.stage;  // the draws are evaluated after the window's last staged row has been taken
     rs.warp_tot = warp_tot;
-    uint32_t *sh_e0 = rs.rank;  // (the single scan keeps ranks in registers: this array parks the exit mask)
     const unsigned gb = pool.plane_groups[0], gg = pool.plane_groups[1];
     const size_t words = (size_t)16 * items;
     uint32_t *board = a.board + i * words, *goals = a.goals + i * words;
@@ -688,9 +687,14 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
     const int level = shst.level_id;
     const uint64_t env = a.env_id0 + (uint64_t)i;
     const int per = items / ROWS_THREADS, i0 = threadIdx.x * per;
-    {
-        const uint32_t *e0 = pool.exit_mask + (size_t)level * items;
-        for (int k = 0; k < per; k++) sh_e0[i0 + k] = e0[i0 + k];  // read back by the same thread only
+    // which of this thread's items hold exit cells (a level has a handful): looked up now, while nothing waits
+    // for it, so that the repaint at the end of the step touches the exit mask only for those
+    const uint32_t *e0 = pool.exit_mask + (size_t)level * items;
+    uint32_t exit_items = 0;
+    if (per <= 32) {
+        for (int k = 0; k < per; k++) exit_items |= (e0[i0 + k] != 0u) ? (1u << k) : 0u;
+    } else {
+        exit_items = 0xffffffffu;  // (more than 32 items per thread: every item is looked at again)
     }
     if (threadIdx.x == 32) { sh_prob = pool.spawn_prob[level]; sh_baseline = pool.baseline[level]; }
     if (threadIdx.x < 32) {
@@ -729,9 +733,10 @@ __device__ __forceinline__ void rows_step_body(const slb_pool &pool, const BigAr
     big_sum3(pts, cur, pos, scratch);  // (its barriers also order the score's reads before the repaint)
     const int completed = cur - sh_baseline, possible = pos - sh_baseline;
     const int ce = can_exit_rule(shst.min_performance, completed, possible);
-    // update_exit_colors (safelife_game.py:531-537) from the parked exit mask
-    for (int k = 0; k < per; k++) {
-        const uint32_t m = sh_e0[i0 + k];
+    // update_exit_colors (safelife_game.py:531-537)
+    for (int k = 0; exit_items != 0u && k < per; k++) {
+        if (per <= 32 && !((exit_items >> k) & 1u)) continue;
+        const uint32_t m = __ldg(e0 + i0 + k);
         if (!m) continue;
         uint32_t P[16];
         big_load(board, g, i0 + k, gb, P);
