@@ -52,4 +52,12 @@ for a in gu.ARCHIVES:
 for (h, w) in [(26, 26), (32, 32), (7, 31), (31, 7), (4, 4), (12, 64), (33, 96), (5, 5), (3, 7), (50, 45)]:
     rng = np.random.RandomState(h * 131 + w)
     run("random %dx%d" % (h, w), _random_levels(rng, 16, h, w), h + w, True, 29, n=96, steps=min(steps, 200))
+# the sliding-window shapes (rows of 2 / 4 / 8 words): fused step kernel of slb_big_rows.cuh
+for (h, w) in [(256, 256), (128, 128), (256, 64), (192, 128), (384, 64)]:
+    rng = np.random.RandomState(h * 131 + w)
+    lv = _random_levels(rng, 6, h, w, exits=16)
+    if h == 256:  # spawners in the goals too: the separate score pass
+        m = rng.rand(*lv["goals"].shape)
+        lv["goals"][m < 0.01] = 1688
+    run("random %dx%d" % (h, w), lv, h + w, True, 23, n=24, steps=min(steps, 150))
 print("SOAK OK")
